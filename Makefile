@@ -1,0 +1,23 @@
+# Builds libb200df.so (sm_100a only) in-tree; `python __graft_entry__.py` / build() calls this.
+NVCC ?= /usr/local/cuda/bin/nvcc
+SRC_DIR := deepfakedetection_b200/csrc
+OUT := deepfakedetection_b200/libb200df.so
+SRCS := $(SRC_DIR)/engine.cu $(SRC_DIR)/stem.cu $(SRC_DIR)/dwconv.cu $(SRC_DIR)/se.cu \
+        $(SRC_DIR)/pwconv_simt.cu $(SRC_DIR)/pwconv_tc.cu $(SRC_DIR)/tail.cu
+OBJS := $(SRCS:.cu=.o)
+HDRS := $(wildcard $(SRC_DIR)/*.h) $(wildcard $(SRC_DIR)/*.cuh) include/b200df.h
+NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC \
+           -Xcompiler -fvisibility=hidden --expt-relaxed-constexpr -cudart static
+
+all: $(OUT)
+
+%.o: %.cu $(HDRS)
+	$(NVCC) $(NVFLAGS) -Xptxas -v -c $< -o $@ 2> $@.ptxas.log || (cat $@.ptxas.log; exit 1)
+
+$(OUT): $(OBJS)
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -cudart static -o $@ $(OBJS)
+
+clean:
+	rm -f $(OBJS) $(SRC_DIR)/*.ptxas.log $(OUT)
+
+.PHONY: all clean

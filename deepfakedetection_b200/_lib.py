@@ -1,0 +1,111 @@
+"""ctypes binding of ``libb200df.so`` (the C ABI declared in ``include/b200df.h``).
+
+There is deliberately no fallback: if the shared library has not been built
+(``python __graft_entry__.py build`` / ``make``) importing the compute path
+raises, and every compute call raises if no sm_100 device is present.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+_PKG = Path(__file__).resolve().parent
+REPO_ROOT = _PKG.parent
+LIB_PATH = _PKG / "libb200df.so"
+
+OK = 0
+E_INVALID, E_STATE, E_CUDA, E_NO_DEVICE, E_WORKSPACE = -1, -2, -3, -4, -5
+ARCH_EFFICIENTNET_B0 = 0
+PREC_BF16, PREC_FP32 = 0, 1
+DT_BF16, DT_FP32 = 0, 1
+
+# name -> (restype, argtypes); must list every symbol include/b200df.h declares
+# (tests/test_abi.py parses the header and checks this table and the .so against it).
+_vp, _i, _ll, _sz, _f = C.c_void_p, C.c_int, C.c_longlong, C.c_size_t, C.c_float
+SIGNATURES: dict[str, tuple] = {
+    "b200df_last_error": (C.c_char_p, []),
+    "b200df_abi_version": (_i, []),
+    "b200df_device_count": (_i, []),
+    "b200df_create": (_i, [_i, _i, _i, C.POINTER(_vp)]),
+    "b200df_destroy": (_i, [_vp]),
+    "b200df_set_tensor": (_i, [_vp, C.c_char_p, _vp, _sz, _i]),
+    "b200df_num_tensors": (_i, [_vp]),
+    "b200df_tensor_info": (_i, [_vp, _i, C.POINTER(C.c_char_p), C.POINTER(_sz)]),
+    "b200df_finalize": (_i, [_vp, _i]),
+    "b200df_workspace_bytes": (_i, [_vp, _i, _i, C.POINTER(_sz)]),
+    "b200df_forward": (_i, [_vp, _vp, _i, _vp, _vp, _sz, _vp]),
+    "b200df_forward_u8": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "b200df_forward_cam": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "b200df_trunk": (_i, [_vp, _vp, _i, _vp, _vp, _sz, _vp]),
+    "b200df_head": (_i, [_vp, _vp, _i, _vp, _vp]),
+    "b200df_head_backward": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "b200df_softmax_pack": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
+    "b200df_launch_count": (_ll, []),
+    "b200df_reset_launch_count": (None, []),
+    "b200df_k_stem": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
+    "b200df_k_dwconv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp]),
+    "b200df_k_se": (_i, [_vp, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "b200df_k_pwconv": (_i, [_vp, _ll, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _vp]),
+    "b200df_k_head_pool": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
+    "b200df_k_cam": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp]),
+    "b200df_k_cam_upsample": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+}
+
+_lib = None
+
+
+class B200DFError(RuntimeError):
+    """A libb200df call failed (carries the C-side status code)."""
+
+    def __init__(self, code: int, message: str) -> None:
+        super().__init__(f"libb200df error {code}: {message}")
+        self.code = code
+
+
+def build(verbose: bool = False) -> Path:
+    """Compile libb200df.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    cmd = ["make", "-C", str(REPO_ROOT), "-j", str(min(8, os.cpu_count() or 1))]
+    proc = subprocess.run(cmd, capture_output=True, text=True)
+    if proc.returncode != 0:
+        raise RuntimeError(f"building libb200df.so failed:\n{proc.stdout[-4000:]}\n{proc.stderr[-4000:]}")
+    if verbose:
+        print(proc.stdout[-2000:])
+    return LIB_PATH
+
+
+def lib() -> C.CDLL:
+    """Load the library once and install the prototypes."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python __graft_entry__.py build` (or `make`). "
+            "deepfakedetection_b200 has no CPU or PyTorch fallback for its compute path."
+        )
+    handle = C.CDLL(str(LIB_PATH))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(handle, name)
+        fn.restype = res
+        fn.argtypes = args
+    if handle.b200df_abi_version() != 1:
+        raise ImportError("libb200df.so ABI version mismatch; rebuild it")
+    _lib = handle
+    return handle
+
+
+def check(code: int) -> None:
+    if code != OK:
+        msg = lib().b200df_last_error()
+        raise B200DFError(code, msg.decode("utf-8", "replace") if msg else "")
+
+
+def launch_count() -> int:
+    return int(lib().b200df_launch_count())
+
+
+def reset_launch_count() -> None:
+    lib().b200df_reset_launch_count()

@@ -1,0 +1,754 @@
+// libb200df.so C-ABI implementation (see include/b200df.h for the contract and the reference
+// interfaces each entry point replaces).
+#include "engine.h"
+
+#include <cuda_bf16.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/b200df.h"
+
+using namespace b200df;
+
+// ---- error / launch-count plumbing --------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static thread_local long long g_launches = 0;
+
+namespace b200df {
+void count_launch(int n) { g_launches += n; }
+}  // namespace b200df
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CU_OK(expr)                                                                         \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess) return fail(B200DF_E_CUDA, "%s failed: %s (%s:%d)", #expr,       \
+                                       cudaGetErrorString(_e), __FILE__, __LINE__);         \
+  } while (0)
+
+extern "C" const char* b200df_last_error(void) { return g_err; }
+extern "C" int b200df_abi_version(void) { return B200DF_ABI_VERSION; }
+extern "C" long long b200df_launch_count(void) { return g_launches; }
+extern "C" void b200df_reset_launch_count(void) { g_launches = 0; }
+
+extern "C" int b200df_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  int ok = 0;
+  for (int i = 0; i < n; ++i) {
+    int major = 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, i) == cudaSuccess && major == 10) ++ok;
+  }
+  return ok;
+}
+
+static int require_sm100(int device) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(B200DF_E_NO_DEVICE, "no CUDA device visible: libb200df has no CPU fallback");
+  }
+  if (device < 0 || device >= n) return fail(B200DF_E_INVALID, "device %d out of range (%d visible)", device, n);
+  int major = 0;
+  CU_OK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+  if (major != 10)
+    return fail(B200DF_E_NO_DEVICE, "device %d has compute capability %d.x; kernels are sm_100a only", device, major);
+  return B200DF_OK;
+}
+
+// ---- EfficientNet-B0 description (timm layout) ---------------------------
+static void add_slot(b200df_engine* e, const std::string& name, size_t numel) {
+  TensorSlot s;
+  s.name = name;
+  s.numel = numel;
+  e->slot_index[name] = (int)e->slots.size();
+  e->slots.push_back(std::move(s));
+}
+static void add_bn(b200df_engine* e, const std::string& p, int c) {
+  add_slot(e, p + ".weight", c);
+  add_slot(e, p + ".bias", c);
+  add_slot(e, p + ".running_mean", c);
+  add_slot(e, p + ".running_var", c);
+}
+
+static void describe_effnet_b0(b200df_engine* e) {
+  struct Stage { bool ds; int k, s, exp, cout, reps; };
+  static const Stage stages[7] = {{true, 3, 1, 1, 16, 1},  {false, 3, 2, 6, 24, 2},  {false, 5, 2, 6, 40, 2},
+                                  {false, 3, 2, 6, 80, 3}, {false, 5, 1, 6, 112, 3}, {false, 5, 2, 6, 192, 4},
+                                  {false, 3, 1, 6, 320, 1}};
+  add_slot(e, "conv_stem.weight", 32 * 27);
+  add_bn(e, "bn1", 32);
+  int cin = 32, h = e->img / 2;
+  for (int s = 0; s < 7; ++s) {
+    for (int r = 0; r < stages[s].reps; ++r) {
+      BlockCfg b;
+      b.prefix = "blocks." + std::to_string(s) + "." + std::to_string(r) + ".";
+      b.expand = !stages[s].ds;
+      b.cin = cin;
+      b.cout = stages[s].cout;
+      b.mid = b.expand ? cin * stages[s].exp : cin;
+      b.k = stages[s].k;
+      b.stride = r == 0 ? stages[s].s : 1;
+      b.skip = (b.stride == 1 && b.cin == b.cout);
+      b.rd = cin / 4 > 0 ? cin / 4 : 1;
+      b.hin = h;
+      b.hout = (h + 2 * ((b.k - 1) / 2) - b.k) / b.stride + 1;
+      const std::string& p = b.prefix;
+      if (b.expand) {
+        add_slot(e, p + "conv_pw.weight", (size_t)b.mid * b.cin);
+        add_bn(e, p + "bn1", b.mid);
+        add_slot(e, p + "conv_dw.weight", (size_t)b.mid * b.k * b.k);
+        add_bn(e, p + "bn2", b.mid);
+      } else {
+        add_slot(e, p + "conv_dw.weight", (size_t)b.mid * b.k * b.k);
+        add_bn(e, p + "bn1", b.mid);
+      }
+      add_slot(e, p + "se.conv_reduce.weight", (size_t)b.rd * b.mid);
+      add_slot(e, p + "se.conv_reduce.bias", b.rd);
+      add_slot(e, p + "se.conv_expand.weight", (size_t)b.mid * b.rd);
+      add_slot(e, p + "se.conv_expand.bias", b.mid);
+      if (b.expand) {
+        add_slot(e, p + "conv_pwl.weight", (size_t)b.cout * b.mid);
+        add_bn(e, p + "bn3", b.cout);
+      } else {
+        add_slot(e, p + "conv_pw.weight", (size_t)b.cout * b.mid);
+        add_bn(e, p + "bn2", b.cout);
+      }
+      e->blocks.push_back(b);
+      cin = b.cout;
+      h = b.hout;
+    }
+  }
+  add_slot(e, "conv_head.weight", (size_t)1280 * cin);
+  add_bn(e, "bn2", 1280);
+  add_slot(e, "classifier.weight", (size_t)e->num_classes * 1280);
+  add_slot(e, "classifier.bias", e->num_classes);
+}
+
+// ---- lifecycle ----------------------------------------------------------------------------------------
+extern "C" int b200df_create(int arch, int num_classes, int device, b200df_handle* out) {
+  if (!out) return fail(B200DF_E_INVALID, "out is NULL");
+  *out = nullptr;
+  if (arch != B200DF_ARCH_EFFICIENTNET_B0) return fail(B200DF_E_INVALID, "unknown arch id %d", arch);
+  if (num_classes < 1 || num_classes > 4096) return fail(B200DF_E_INVALID, "num_classes %d out of range", num_classes);
+  // No device is needed to describe a model (tests list the expected tensors on CPU boxes);
+  // finalize() and every compute entry point require an sm_100 device and never fall back.
+  b200df_engine* e = new b200df_engine();
+  e->arch = arch;
+  e->num_classes = num_classes;
+  e->device = device;
+  describe_effnet_b0(e);
+  *out = e;
+  return B200DF_OK;
+}
+
+static void free_device(b200df_engine* e) {
+  if (e->arena) {
+    cudaFree(e->arena);
+    e->arena = nullptr;
+  }
+  e->bdev.clear();
+  e->plan = Plan();
+  e->precision = -1;
+}
+
+extern "C" int b200df_destroy(b200df_handle h) {
+  if (!h) return B200DF_OK;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  cudaSetDevice(h->device);
+  free_device(h);
+  cudaSetDevice(prev);
+  delete h;
+  return B200DF_OK;
+}
+
+extern "C" int b200df_num_tensors(b200df_handle h) { return h ? (int)h->slots.size() : 0; }
+
+extern "C" int b200df_tensor_info(b200df_handle h, int index, const char** name, size_t* numel) {
+  if (!h || index < 0 || index >= (int)h->slots.size()) return fail(B200DF_E_INVALID, "tensor index out of range");
+  if (name) *name = h->slots[index].name.c_str();
+  if (numel) *numel = h->slots[index].numel;
+  return B200DF_OK;
+}
+
+extern "C" int b200df_set_tensor(b200df_handle h, const char* name, const float* data, size_t numel, int is_device) {
+  if (!h || !name || !data) return fail(B200DF_E_INVALID, "NULL argument");
+  auto it = h->slot_index.find(name);
+  if (it == h->slot_index.end()) return fail(B200DF_E_INVALID, "unknown tensor '%s'", name);
+  TensorSlot& s = h->slots[it->second];
+  if (numel != s.numel)
+    return fail(B200DF_E_INVALID, "tensor '%s': got %zu elements, expected %zu", name, numel, s.numel);
+  s.host.resize(numel);
+  if (is_device) {
+    CU_OK(cudaMemcpy(s.host.data(), data, numel * sizeof(float), cudaMemcpyDeviceToHost));
+  } else {
+    memcpy(s.host.data(), data, numel * sizeof(float));
+  }
+  s.set = true;
+  return B200DF_OK;
+}
+
+// ---- finalize: fold BN (fp32, host), convert, lay out, upload -----------------------------------------
+namespace {
+
+struct Packer {
+  std::vector<uint8_t> buf;
+  size_t alloc(size_t bytes) {
+    size_t off = (buf.size() + 1023) & ~size_t(1023);
+    buf.resize(off + bytes, 0);
+    return off;
+  }
+};
+
+inline uint16_t f2bf(float f) {  // round-to-nearest-even, like __float2bfloat16_rn
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);  // NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+
+const std::vector<float>& T(const b200df_engine* e, const std::string& name) {
+  return e->slots[e->slot_index.at(name)].host;
+}
+
+// BN(eval): y = (x - mean)/sqrt(var + eps)*gamma + beta  ->  scale, shift
+void bn_fold(const b200df_engine* e, const std::string& p, int c, std::vector<float>& scale, std::vector<float>& shift) {
+  const auto& g = T(e, p + ".weight");
+  const auto& b = T(e, p + ".bias");
+  const auto& m = T(e, p + ".running_mean");
+  const auto& v = T(e, p + ".running_var");
+  scale.resize(c);
+  shift.resize(c);
+  for (int i = 0; i < c; ++i) {
+    float s = g[i] / sqrtf(v[i] + 1e-5f);
+    scale[i] = s;
+    shift[i] = b[i] - m[i] * s;
+  }
+}
+
+int choose_bn(int cout, int* cout_pad) {
+  int pad = (cout + 15) / 16 * 16;
+  if (pad <= 256) {
+    *cout_pad = pad;
+    return pad;
+  }
+  for (int t = 2; t <= 64; ++t) {
+    if (pad % (16 * t) == 0 && pad / t <= 256) {
+      *cout_pad = pad;
+      return pad / t;
+    }
+  }
+  int t = (pad + 255) / 256;
+  int bn = ((pad + t - 1) / t + 15) / 16 * 16;
+  *cout_pad = bn * t;
+  return bn;
+}
+
+struct PwOff { size_t w, bias; };
+
+// w_src: [cout, cin] fp32; scale may be empty (no fold); shift -> bias (empty -> zeros)
+PwOff pack_pw(Packer& pk, PwLayer& L, const std::vector<float>& w_src, int cout, int cin,
+              const std::vector<float>& scale, const std::vector<float>& shift, int precision) {
+  L.cin = cin;
+  L.cout = cout;
+  L.bn = choose_bn(cout, &L.cout_pad);
+  const size_t es = precision == B200DF_PREC_BF16 ? 2 : 4;
+  PwOff o;
+  o.w = pk.alloc((size_t)L.cout_pad * cin * es);
+  o.bias = pk.alloc((size_t)L.cout_pad * sizeof(float));
+  for (int oc = 0; oc < cout; ++oc) {
+    const float s = scale.empty() ? 1.0f : scale[oc];
+    for (int k = 0; k < cin; ++k) {
+      float v = w_src[(size_t)oc * cin + k] * s;
+      if (es == 2) reinterpret_cast<uint16_t*>(pk.buf.data() + o.w)[(size_t)oc * cin + k] = f2bf(v);
+      else reinterpret_cast<float*>(pk.buf.data() + o.w)[(size_t)oc * cin + k] = v;
+    }
+    reinterpret_cast<float*>(pk.buf.data() + o.bias)[oc] = shift.empty() ? 0.0f : shift[oc];
+  }
+  return o;
+}
+
+size_t pack_f32(Packer& pk, const std::vector<float>& v) {
+  size_t off = pk.alloc(v.size() * sizeof(float));
+  memcpy(pk.buf.data() + off, v.data(), v.size() * sizeof(float));
+  return off;
+}
+
+}  // namespace
+
+extern "C" int b200df_finalize(b200df_handle h, int precision) {
+  if (!h) return fail(B200DF_E_INVALID, "NULL handle");
+  if (precision != B200DF_PREC_BF16 && precision != B200DF_PREC_FP32)
+    return fail(B200DF_E_INVALID, "unknown precision %d", precision);
+  for (const auto& s : h->slots)
+    if (!s.set) return fail(B200DF_E_STATE, "tensor '%s' was never provided (set_tensor)", s.name.c_str());
+  int rc = require_sm100(h->device);
+  if (rc != B200DF_OK) return rc;
+  CU_OK(cudaSetDevice(h->device));
+  free_device(h);
+
+  Packer pk;
+  std::vector<float> sc, sh, tmp;
+  // stem
+  bn_fold(h, "bn1", 32, sc, sh);
+  tmp = T(h, "conv_stem.weight");
+  for (int oc = 0; oc < 32; ++oc)
+    for (int t = 0; t < 27; ++t) tmp[oc * 27 + t] *= sc[oc];
+  const size_t stem_w = pack_f32(pk, tmp), stem_b = pack_f32(pk, sh);
+
+  struct BOff { PwOff ex, pr; size_t dw_w, dw_b, w1, b1, w2t, b2; };
+  std::vector<BOff> boff(h->blocks.size());
+  h->bdev.assign(h->blocks.size(), BlockDev());
+  size_t pool_off = 0;
+  for (size_t i = 0; i < h->blocks.size(); ++i) {
+    const BlockCfg& b = h->blocks[i];
+    BlockDev& d = h->bdev[i];
+    const std::string& p = b.prefix;
+    if (b.expand) {
+      bn_fold(h, p + "bn1", b.mid, sc, sh);
+      boff[i].ex = pack_pw(pk, d.expand, T(h, p + "conv_pw.weight"), b.mid, b.cin, sc, sh, precision);
+    }
+    // depthwise: [mid,1,k,k] -> tap-major [k*k, mid], BN folded
+    bn_fold(h, p + (b.expand ? "bn2" : "bn1"), b.mid, sc, sh);
+    {
+      const auto& w = T(h, p + "conv_dw.weight");
+      const int kk = b.k * b.k;
+      tmp.assign((size_t)kk * b.mid, 0.f);
+      for (int c = 0; c < b.mid; ++c)
+        for (int t = 0; t < kk; ++t) tmp[(size_t)t * b.mid + c] = w[(size_t)c * kk + t] * sc[c];
+      boff[i].dw_w = pack_f32(pk, tmp);
+      boff[i].dw_b = pack_f32(pk, sh);
+    }
+    // squeeze-excite
+    boff[i].w1 = pack_f32(pk, T(h, p + "se.conv_reduce.weight"));
+    boff[i].b1 = pack_f32(pk, T(h, p + "se.conv_reduce.bias"));
+    {
+      const auto& w2 = T(h, p + "se.conv_expand.weight");  // [mid, rd]
+      tmp.assign((size_t)b.rd * b.mid, 0.f);
+      for (int c = 0; c < b.mid; ++c)
+        for (int j = 0; j < b.rd; ++j) tmp[(size_t)j * b.mid + c] = w2[(size_t)c * b.rd + j];
+      boff[i].w2t = pack_f32(pk, tmp);
+    }
+    boff[i].b2 = pack_f32(pk, T(h, p + "se.conv_expand.bias"));
+    // project
+    bn_fold(h, p + (b.expand ? "bn3" : "bn2"), b.cout, sc, sh);
+    boff[i].pr = pack_pw(pk, d.project, T(h, p + (b.expand ? "conv_pwl.weight" : "conv_pw.weight")), b.cout, b.mid,
+                         sc, sh, precision);
+    d.pool_off = pool_off;
+    pool_off += (size_t)b.mid;
+  }
+  h->pool_floats_per_img = pool_off;
+  // head: conv_head stays un-folded (its raw output is the Grad-CAM activation); bn2 -> scale/shift
+  const int cin_head = h->blocks.back().cout;
+  PwOff head_off = pack_pw(pk, h->head, T(h, "conv_head.weight"), 1280, cin_head, {}, {}, precision);
+  bn_fold(h, "bn2", 1280, sc, sh);
+  const size_t hs = pack_f32(pk, sc), hb = pack_f32(pk, sh);
+  const size_t fw = pack_f32(pk, T(h, "classifier.weight")), fb = pack_f32(pk, T(h, "classifier.bias"));
+
+  h->arena_bytes = (pk.buf.size() + 1023) & ~size_t(1023);
+  CU_OK(cudaMalloc(&h->arena, h->arena_bytes));
+  CU_OK(cudaMemcpy(h->arena, pk.buf.data(), pk.buf.size(), cudaMemcpyHostToDevice));
+  uint8_t* base = reinterpret_cast<uint8_t*>(h->arena);
+  auto F = [&](size_t off) { return reinterpret_cast<float*>(base + off); };
+  h->stem_w = F(stem_w);
+  h->stem_b = F(stem_b);
+  for (size_t i = 0; i < h->blocks.size(); ++i) {
+    BlockDev& d = h->bdev[i];
+    if (h->blocks[i].expand) {
+      d.expand.w = base + boff[i].ex.w;
+      d.expand.bias = F(boff[i].ex.bias);
+    }
+    d.project.w = base + boff[i].pr.w;
+    d.project.bias = F(boff[i].pr.bias);
+    d.dw_w = F(boff[i].dw_w);
+    d.dw_b = F(boff[i].dw_b);
+    d.se_w1 = F(boff[i].w1);
+    d.se_b1 = F(boff[i].b1);
+    d.se_w2t = F(boff[i].w2t);
+    d.se_b2 = F(boff[i].b2);
+  }
+  h->head.w = base + head_off.w;
+  h->head.bias = F(head_off.bias);
+  h->head_scale = F(hs);
+  h->head_shift = F(hb);
+  h->fc_w = F(fw);
+  h->fc_b = F(fb);
+  h->precision = precision;
+  h->gemm_impl = precision == B200DF_PREC_BF16 ? 0 : 1;
+  if (const char* env = getenv("B200DF_GEMM")) {  // debugging aid: force the SIMT GEMM on the bf16 path
+    if (strcmp(env, "simt") == 0) h->gemm_impl = 1;
+  }
+  return B200DF_OK;
+}
+
+// ---- workspace ------------------------------------------------------------------------------------------
+static Workspace layout_workspace(const b200df_engine* h, int n) {
+  const size_t es = h->precision == B200DF_PREC_BF16 ? 2 : 4;
+  size_t trunk = (size_t)32 * (h->img / 2) * (h->img / 2);  // stem output
+  size_t e = 0, d = 0;
+  for (const auto& b : h->blocks) {
+    trunk = std::max(trunk, (size_t)b.cout * b.hout * b.hout);
+    if (b.expand) e = std::max(e, (size_t)b.mid * b.hin * b.hin);
+    d = std::max(d, (size_t)b.mid * b.hout * b.hout);
+  }
+  const int hw = h->blocks.back().hout * h->blocks.back().hout;
+  auto al = [](size_t x) { return (x + 1023) & ~size_t(1023); };
+  Workspace w;
+  size_t off = 0;
+  w.t0 = off; off += al(trunk * n * es);
+  w.t1 = off; off += al(trunk * n * es);
+  w.e = off; off += al(e * n * es);
+  w.d = off; off += al(d * n * es);
+  w.a = off; off += al((size_t)1280 * hw * n * es);
+  w.pool = off; off += al(h->pool_floats_per_img * n * sizeof(float));
+  w.gate = off; off += al(h->pool_floats_per_img * n * sizeof(float));
+  w.pooled = off; off += al((size_t)1280 * n * sizeof(float));
+  w.logits = off; off += al((size_t)h->num_classes * n * sizeof(float));
+  w.cam_low = off; off += al((size_t)hw * n * sizeof(float));
+  w.total = off;
+  return w;
+}
+
+extern "C" int b200df_workspace_bytes(b200df_handle h, int n, int mode, size_t* bytes) {
+  (void)mode;
+  if (!h || !bytes || n < 0) return fail(B200DF_E_INVALID, "bad argument");
+  if (h->precision < 0) return fail(B200DF_E_STATE, "b200df_finalize has not been called");
+  *bytes = layout_workspace(h, n > 0 ? n : 1).total;
+  return B200DF_OK;
+}
+
+// ---- forward schedule ---------------------------------------------------------------------------------------
+namespace {
+
+struct GemmCall {  // one pointwise conv in schedule order
+  const PwLayer* L;
+  const void* x;
+  long long m;
+  const float* gate;
+  int rows_per_img;
+  const void* residual;
+  int act;
+  void* out;
+};
+
+int run_gemm(b200df_engine* h, const GemmCall& g, int index, cudaStream_t s) {
+  const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
+  if (h->gemm_impl == 1) {
+    CU_OK(launch_pwconv_simt(g.x, g.m, g.L->cin, g.L->cout, g.L->w, g.L->bias, g.gate, g.rows_per_img, g.residual,
+                             g.act, g.out, dt, s));
+    return B200DF_OK;
+  }
+  if ((int)h->plan.gemms.size() <= index) h->plan.gemms.resize(index + 1);
+  TcGemmArgs& a = h->plan.gemms[index];
+  if (a.out != g.out || a.m != g.m) {  // (re)encode tensor maps for this (n, workspace)
+    memset(&a, 0, sizeof(a));
+    int r1 = encode_tmap_2d_bf16(a.tmap_a, g.x, g.m, g.L->cin, 128);
+    int r2 = encode_tmap_2d_bf16(a.tmap_b, g.L->w, g.L->cout_pad, g.L->cin, g.L->bn);
+    if (r1 || r2) return fail(B200DF_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d) for gemm %d", r1, r2, index);
+    a.m = g.m;
+    a.cin = g.L->cin;
+    a.cout = g.L->cout;
+    a.cout_pad = g.L->cout_pad;
+    a.bn = g.L->bn;
+    a.bias = g.L->bias;
+    a.gate = g.gate;
+    a.rows_per_img = g.rows_per_img;
+    a.residual = g.residual;
+    a.act = g.act;
+    a.out = g.out;
+  }
+  CU_OK(launch_pwconv_tc(a, s));
+  return B200DF_OK;
+}
+
+enum InputKind { kInF32NCHW = 0, kInU8HWC = 1 };
+
+// Runs stem -> 16 MBConv blocks -> conv_head.  Leaves A (raw conv_head output, NHWC) in ws.a.
+int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in_sc, const float* in_sh, int n,
+              uint8_t* ws, const Workspace& W, cudaStream_t s) {
+  const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
+  if (h->plan.n != n || h->plan.ws != ws) {
+    h->plan = Plan();
+    h->plan.n = n;
+    h->plan.ws = ws;
+  }
+  float* pool = reinterpret_cast<float*>(ws + W.pool);
+  float* gate = reinterpret_cast<float*>(ws + W.gate);
+  CU_OK(cudaMemsetAsync(pool, 0, h->pool_floats_per_img * n * sizeof(float), s));
+  void* cur = ws + W.t0;
+  void* nxt = ws + W.t1;
+  if (in_kind == kInF32NCHW) {
+    CU_OK(launch_stem(reinterpret_cast<const float*>(images), n, h->img, h->img, h->stem_w, h->stem_b, cur, dt, s));
+  } else {
+    CU_OK(launch_stem_u8(reinterpret_cast<const uint8_t*>(images), n, h->img, h->img, h->stem_w, h->stem_b, in_sc[0],
+                         in_sc[1], in_sc[2], in_sh[0], in_sh[1], in_sh[2], cur, dt, s));
+  }
+  int gi = 0;
+  for (size_t i = 0; i < h->blocks.size(); ++i) {
+    const BlockCfg& b = h->blocks[i];
+    const BlockDev& d = h->bdev[i];
+    const long long m_in = (long long)n * b.hin * b.hin, m_out = (long long)n * b.hout * b.hout;
+    const void* dw_in = cur;
+    if (b.expand) {
+      GemmCall g{&d.expand, cur, m_in, nullptr, 1, nullptr, 1, ws + W.e};
+      int rc = run_gemm(h, g, gi++, s);
+      if (rc) return rc;
+      dw_in = ws + W.e;
+    }
+    float* pool_b = pool + d.pool_off * n;
+    float* gate_b = gate + d.pool_off * n;
+    CU_OK(launch_dwconv(dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b, dt, s));
+    CU_OK(launch_se(pool_b, n, b.mid, b.rd, 1.0f / (float)(b.hout * b.hout), d.se_w1, d.se_b1, d.se_w2t, d.se_b2,
+                    gate_b, s));
+    GemmCall g{&d.project, ws + W.d, m_out, gate_b, b.hout * b.hout, b.skip ? cur : nullptr, 0, nxt};
+    int rc = run_gemm(h, g, gi++, s);
+    if (rc) return rc;
+    std::swap(cur, nxt);
+  }
+  const int hw = h->blocks.back().hout * h->blocks.back().hout;
+  GemmCall g{&h->head, cur, (long long)n * hw, nullptr, 1, nullptr, 0, ws + W.a};
+  return run_gemm(h, g, gi++, s);
+}
+
+int check_call(b200df_engine* h, int n, const void* ws, size_t ws_bytes, Workspace* W) {
+  if (!h) return fail(B200DF_E_INVALID, "NULL handle");
+  if (h->precision < 0) return fail(B200DF_E_STATE, "b200df_finalize has not been called");
+  if (n < 0) return fail(B200DF_E_INVALID, "negative batch");
+  *W = layout_workspace(h, n > 0 ? n : 1);
+  if (n > 0) {
+    if (!ws || (reinterpret_cast<uintptr_t>(ws) & 1023))
+      return fail(B200DF_E_WORKSPACE, "workspace must be non-NULL and 1024-byte aligned");
+    if (ws_bytes < W->total)
+      return fail(B200DF_E_WORKSPACE, "workspace too small: %zu < %zu bytes for n=%d", ws_bytes, W->total, n);
+  }
+  return B200DF_OK;
+}
+
+int run_head(b200df_engine* h, int n, uint8_t* ws, const Workspace& W, float* logits, cudaStream_t s) {
+  const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
+  const int hw = h->blocks.back().hout * h->blocks.back().hout;
+  float* pooled = reinterpret_cast<float*>(ws + W.pooled);
+  CU_OK(launch_head_pool(ws + W.a, n, hw, 1280, h->head_scale, h->head_shift, pooled, dt, s));
+  CU_OK(launch_classifier(pooled, n, 1280, h->fc_w, h->fc_b, h->num_classes, logits, s));
+  return B200DF_OK;
+}
+
+}  // namespace
+
+extern "C" int b200df_forward(b200df_handle h, const float* images, int n, float* logits, void* workspace,
+                              size_t workspace_bytes, void* stream) {
+  Workspace W;
+  int rc = check_call(h, n, workspace, workspace_bytes, &W);
+  if (rc || n == 0) return rc;
+  if (!images || !logits) return fail(B200DF_E_INVALID, "NULL images/logits");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  rc = run_trunk(h, images, kInF32NCHW, nullptr, nullptr, n, ws, W, s);
+  if (rc) return rc;
+  return run_head(h, n, ws, W, logits, s);
+}
+
+extern "C" int b200df_forward_u8(b200df_handle h, const uint8_t* images_hwc, int n, const float* mean,
+                                 const float* stdv, float* logits, void* workspace, size_t workspace_bytes,
+                                 void* stream) {
+  Workspace W;
+  int rc = check_call(h, n, workspace, workspace_bytes, &W);
+  if (rc || n == 0) return rc;
+  if (!images_hwc || !logits) return fail(B200DF_E_INVALID, "NULL images/logits");
+  float sc[3], sh[3];
+  for (int c = 0; c < 3; ++c) {  // ToTensor: /255; Normalize: (x - mean)/std  (orchestrator.py:340-345)
+    float sd = stdv ? stdv[c] : 1.0f, mu = mean ? mean[c] : 0.0f;
+    sc[c] = 1.0f / (255.0f * sd);
+    sh[c] = -mu / sd;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  rc = run_trunk(h, images_hwc, kInU8HWC, sc, sh, n, ws, W, s);
+  if (rc) return rc;
+  return run_head(h, n, ws, W, logits, s);
+}
+
+extern "C" int b200df_forward_cam(b200df_handle h, const float* images, int n, const int32_t* target_cls,
+                                  float* logits, float* cam_lowres, float* cam, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+  Workspace W;
+  int rc = check_call(h, n, workspace, workspace_bytes, &W);
+  if (rc || n == 0) return rc;
+  if (!images) return fail(B200DF_E_INVALID, "NULL images");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
+  const int side = h->blocks.back().hout, hw = side * side;
+  rc = run_trunk(h, images, kInF32NCHW, nullptr, nullptr, n, ws, W, s);
+  if (rc) return rc;
+  float* lg = logits ? logits : reinterpret_cast<float*>(ws + W.logits);
+  rc = run_head(h, n, ws, W, lg, s);
+  if (rc) return rc;
+  float* low = cam_lowres ? cam_lowres : reinterpret_cast<float*>(ws + W.cam_low);
+  CU_OK(launch_cam(ws + W.a, n, hw, 1280, h->head_scale, h->head_shift, h->fc_w, h->num_classes, target_cls, lg, low,
+                   dt, s));
+  if (cam) CU_OK(launch_cam_upsample(low, n, side, h->img, cam, s));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_trunk(b200df_handle h, const float* images, int n, float* a_nchw, void* workspace,
+                            size_t workspace_bytes, void* stream) {
+  Workspace W;
+  int rc = check_call(h, n, workspace, workspace_bytes, &W);
+  if (rc || n == 0) return rc;
+  if (!images || !a_nchw) return fail(B200DF_E_INVALID, "NULL images/output");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
+  const int hw = h->blocks.back().hout * h->blocks.back().hout;
+  rc = run_trunk(h, images, kInF32NCHW, nullptr, nullptr, n, ws, W, s);
+  if (rc) return rc;
+  CU_OK(launch_nhwc_to_nchw_f32(ws + W.a, n, hw, 1280, a_nchw, dt, s));
+  return B200DF_OK;
+}
+
+// Scratch for the split head: pooled [n,1280] lives in a small per-engine cache grown on demand
+// (outside stream capture), so head()/head_backward() need no caller workspace.
+static int head_scratch(b200df_engine* h, int n, float** out) {
+  static thread_local float* buf = nullptr;
+  static thread_local size_t cap = 0;
+  size_t need = (size_t)n * 1280 * sizeof(float);
+  if (need > cap) {
+    if (buf) cudaFree(buf);
+    buf = nullptr;
+    cap = 0;
+    CU_OK(cudaMalloc(&buf, need));
+    cap = need;
+  }
+  (void)h;
+  *out = buf;
+  return B200DF_OK;
+}
+
+extern "C" int b200df_head(b200df_handle h, const float* a_nchw, int n, float* logits, void* stream) {
+  if (!h || h->precision < 0) return fail(B200DF_E_STATE, "engine not finalized");
+  if (n <= 0) return n == 0 ? B200DF_OK : fail(B200DF_E_INVALID, "negative batch");
+  if (!a_nchw || !logits) return fail(B200DF_E_INVALID, "NULL argument");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int hw = h->blocks.back().hout * h->blocks.back().hout;
+  float* pooled = nullptr;
+  int rc = head_scratch(h, n, &pooled);
+  if (rc) return rc;
+  CU_OK(launch_head_from_nchw(a_nchw, n, hw, 1280, h->head_scale, h->head_shift, pooled, s));
+  CU_OK(launch_classifier(pooled, n, 1280, h->fc_w, h->fc_b, h->num_classes, logits, s));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_head_backward(b200df_handle h, const float* a_nchw, const float* grad_logits, int n,
+                                    float* grad_a_nchw, void* stream) {
+  if (!h || h->precision < 0) return fail(B200DF_E_STATE, "engine not finalized");
+  if (n <= 0) return n == 0 ? B200DF_OK : fail(B200DF_E_INVALID, "negative batch");
+  if (!a_nchw || !grad_logits || !grad_a_nchw) return fail(B200DF_E_INVALID, "NULL argument");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int hw = h->blocks.back().hout * h->blocks.back().hout;
+  CU_OK(launch_head_backward(a_nchw, grad_logits, n, hw, 1280, h->head_scale, h->head_shift, h->fc_w, h->num_classes,
+                             grad_a_nchw, s));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_softmax_pack(const float* logits, const int64_t* labels, int n, int num_classes, float* packed,
+                                   void* stream) {
+  if (n < 0 || num_classes < 1 || (n > 0 && (!logits || !packed))) return fail(B200DF_E_INVALID, "bad argument");
+  CU_OK(launch_softmax_pack(logits, labels, n, num_classes, packed, reinterpret_cast<cudaStream_t>(stream)));
+  return B200DF_OK;
+}
+
+// ---- per-kernel entry points (unit tests / ncu) ---------------------------------------------------------------
+static cudaStream_t S(void* stream) { return reinterpret_cast<cudaStream_t>(stream); }
+
+extern "C" int b200df_k_stem(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias, void* out,
+                             int dtype, void* stream) {
+  CU_OK(launch_stem(x_nchw, n, h, w, wgt, bias, out, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
+                               const float* bias, void* out, float* pool, int dtype, void* stream) {
+  CU_OK(launch_dwconv(x, n, h, w, c, k, stride, wgt, bias, out, pool, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_se(const float* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
+                           const float* w2t, const float* b2, float* gate, void* stream) {
+  CU_OK(launch_se(pool, n, c, rd, inv_hw, w1, b1, w2t, b2, gate, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_pwconv(const void* x, long long m, int cin, int cout, const void* wgt, const float* bias,
+                               const float* gate, int rows_per_img, const void* residual, int act, void* out,
+                               int dtype, int impl, void* stream) {
+  if (impl == 1) {
+    CU_OK(launch_pwconv_simt(x, m, cin, cout, wgt, bias, gate, rows_per_img, residual, act, out, dtype, S(stream)));
+    return B200DF_OK;
+  }
+  if (dtype != kBF16) return fail(B200DF_E_INVALID, "the tcgen05 GEMM is bf16-only");
+  if (cin % 8 || cout % 8) return fail(B200DF_E_INVALID, "cin and cout must be multiples of 8");
+  // test-only convenience: pad weights/bias to the N tile on the fly (the engine does this once in finalize)
+  int cout_pad = 0;
+  const int bn = choose_bn(cout, &cout_pad);
+  void* wpad = nullptr;
+  float* bpad = nullptr;
+  CU_OK(cudaMalloc(&wpad, (size_t)cout_pad * cin * 2));
+  CU_OK(cudaMalloc(&bpad, (size_t)cout_pad * sizeof(float)));
+  cudaStream_t s = S(stream);
+  CU_OK(cudaMemsetAsync(wpad, 0, (size_t)cout_pad * cin * 2, s));
+  CU_OK(cudaMemsetAsync(bpad, 0, (size_t)cout_pad * sizeof(float), s));
+  CU_OK(cudaMemcpyAsync(wpad, wgt, (size_t)cout * cin * 2, cudaMemcpyDeviceToDevice, s));
+  CU_OK(cudaMemcpyAsync(bpad, bias, (size_t)cout * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  TcGemmArgs a;
+  memset(&a, 0, sizeof(a));
+  int r1 = encode_tmap_2d_bf16(a.tmap_a, x, m, cin, 128);
+  int r2 = encode_tmap_2d_bf16(a.tmap_b, wpad, cout_pad, cin, bn);
+  int rc = B200DF_OK;
+  if (r1 || r2) {
+    rc = fail(B200DF_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d)", r1, r2);
+  } else {
+    a.m = m; a.cin = cin; a.cout = cout; a.cout_pad = cout_pad; a.bn = bn;
+    a.bias = bpad; a.gate = gate; a.rows_per_img = rows_per_img; a.residual = residual; a.act = act; a.out = out;
+    cudaError_t e = launch_pwconv_tc(a, s);
+    if (e != cudaSuccess) rc = fail(B200DF_E_CUDA, "launch_pwconv_tc: %s", cudaGetErrorString(e));
+  }
+  cudaError_t es = cudaStreamSynchronize(s);
+  cudaFree(wpad);
+  cudaFree(bpad);
+  if (rc == B200DF_OK && es != cudaSuccess) rc = fail(B200DF_E_CUDA, "pwconv_tc execution: %s", cudaGetErrorString(es));
+  return rc;
+}
+
+extern "C" int b200df_k_head_pool(const void* a, int n, int hw, int c, const float* scale, const float* shift,
+                                  float* pooled, int dtype, void* stream) {
+  CU_OK(launch_head_pool(a, n, hw, c, scale, shift, pooled, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_cam(const void* a, int n, int hw, int c, const float* scale, const float* shift,
+                            const float* wfc, int num_classes, const int32_t* target_cls, float* cam_lowres,
+                            int dtype, void* stream) {
+  if (!target_cls) return fail(B200DF_E_INVALID, "target_cls is required for the standalone CAM kernel");
+  CU_OK(launch_cam(a, n, hw, c, scale, shift, wfc, num_classes, target_cls, nullptr, cam_lowres, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_cam_upsample(const float* cam_lowres, int n, int side, int out_side, float* cam,
+                                     void* stream) {
+  CU_OK(launch_cam_upsample(cam_lowres, n, side, out_side, cam, S(stream)));
+  return B200DF_OK;
+}

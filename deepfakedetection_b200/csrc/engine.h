@@ -1,0 +1,82 @@
+// Engine: host-side model description, weight folding/packing and the forward schedule.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+
+namespace b200df {
+
+struct TensorSlot {
+  std::string name;
+  size_t numel = 0;
+  std::vector<float> host;  // raw fp32 copy as provided by set_tensor
+  bool set = false;
+};
+
+// One MBConv block (timm DepthwiseSeparableConv when !expand, InvertedResidual otherwise).
+struct BlockCfg {
+  std::string prefix;  // "blocks.S.B."
+  bool expand = false;
+  bool skip = false;
+  int cin = 0, mid = 0, cout = 0, k = 3, stride = 1, rd = 0;
+  int hin = 0, hout = 0;  // square spatial sizes
+};
+
+// A packed pointwise-conv (GEMM) layer on the device.
+struct PwLayer {
+  int cin = 0, cout = 0, cout_pad = 0, bn = 0;
+  void* w = nullptr;       // [cout_pad, cin] in the engine dtype (BN scale folded in)
+  float* bias = nullptr;   // [cout_pad] fp32
+};
+
+struct BlockDev {
+  PwLayer expand, project;
+  float* dw_w = nullptr;   // [k*k, mid] fp32, BN folded
+  float* dw_b = nullptr;   // [mid]
+  float* se_w1 = nullptr;  // [rd, mid]
+  float* se_b1 = nullptr;  // [rd]
+  float* se_w2t = nullptr; // [rd, mid] (conv_expand transposed)
+  float* se_b2 = nullptr;  // [mid]
+  size_t pool_off = 0;     // float offset of this block's [n, mid] pool/gate slabs, per image
+};
+
+struct Plan {  // cached tensor maps for one (n, workspace) pair
+  int n = -1;
+  void* ws = nullptr;
+  std::vector<TcGemmArgs> gemms;  // in schedule order
+};
+
+struct Workspace {
+  size_t t0, t1, e, d, a, pool, gate, pooled, logits, cam_low, total;
+};
+
+}  // namespace b200df
+
+struct b200df_engine {
+  int arch = 0, num_classes = 2, device = 0;
+  int precision = -1;  // -1 = not finalized
+  int img = 224;
+  std::vector<b200df::TensorSlot> slots;
+  std::map<std::string, int> slot_index;
+  std::vector<b200df::BlockCfg> blocks;
+  // device weights
+  void* arena = nullptr;
+  size_t arena_bytes = 0;
+  float* stem_w = nullptr;  // [32, 27]
+  float* stem_b = nullptr;  // [32]
+  std::vector<b200df::BlockDev> bdev;
+  b200df::PwLayer head;      // conv_head, raw (no BN fold: its output is the Grad-CAM activation)
+  float* head_scale = nullptr;  // bn2 folded scale/shift [1280]
+  float* head_shift = nullptr;
+  float* fc_w = nullptr;  // [num_classes, 1280]
+  float* fc_b = nullptr;
+  size_t pool_floats_per_img = 0;
+  int gemm_impl = 0;  // 0 = tcgen05 (bf16), 1 = SIMT
+  b200df::Plan plan;
+};

@@ -1,0 +1,76 @@
+// Host-side launcher declarations shared by the engine and the C-ABI per-kernel entry points.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200df {
+
+enum DType : int { kBF16 = 0, kFP32 = 1 };
+inline size_t dtype_size(int dt) { return dt == kBF16 ? 2 : 4; }
+
+// thread-local launch counter (bench.py's gpu_launches)
+void count_launch(int n = 1);
+
+// error plumbing: launchers return cudaError_t of the launch (cudaGetLastError()).
+cudaError_t launch_stem(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias,
+                        void* out, int dtype, cudaStream_t s);
+
+// u8 HWC input, fused ToTensor(/255)+Normalize: in_scale[c] = 1/(255*std[c]), in_shift[c] = -mean[c]/std[c]
+cudaError_t launch_stem_u8(const uint8_t* x_hwc, int n, int h, int w, const float* wgt, const float* bias,
+                           float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, void* out,
+                           int dtype, cudaStream_t s);
+
+cudaError_t launch_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
+                          const float* bias, void* out, float* pool, int dtype, cudaStream_t s);
+
+cudaError_t launch_se(const float* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
+                      const float* w2, const float* b2, float* gate, cudaStream_t s);
+
+cudaError_t launch_pwconv_simt(const void* x, long long m, int cin, int cout, const void* wgt, const float* bias,
+                               const float* gate, int rows_per_img, const void* residual, int act, void* out,
+                               int dtype, cudaStream_t s);
+
+// tcgen05 GEMM.  Tensor maps are encoded by the caller (engine caches them per plan);
+// see pwconv_tc.cu for the layout contract.
+struct TcGemmArgs {
+  // CUtensorMap is 128 bytes, 64-byte aligned; kept opaque here.
+  alignas(64) unsigned char tmap_a[128];
+  alignas(64) unsigned char tmap_b[128];
+  long long m;        // rows of A / out
+  int cin;            // K
+  int cout;           // valid output columns (row pitch of out / residual)
+  int cout_pad;       // rows of the padded weight matrix (multiple of bn)
+  int bn;             // N tile (multiple of 16, <= 256), divides cout_pad
+  const float* bias;  // [cout_pad]
+  const float* gate;  // [m / rows_per_img, cin] or nullptr
+  int rows_per_img;
+  const void* residual;  // bf16 [m, cout] or nullptr
+  int act;               // 0 none, 1 SiLU
+  void* out;             // bf16 [m, cout]
+};
+// Encodes a 2D bf16 row-major [rows, cols] tensor map with box [box_rows, 64] and 128B swizzle.
+int encode_tmap_2d_bf16(void* tmap_out, const void* base, long long rows, int cols, int box_rows);
+cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s);
+
+cudaError_t launch_head_pool(const void* a, int n, int hw, int c, const float* scale, const float* shift,
+                             float* pooled, int dtype, cudaStream_t s);
+cudaError_t launch_classifier(const float* pooled, int n, int c, const float* w, const float* b, int num_classes,
+                              float* logits, cudaStream_t s);
+cudaError_t launch_cam(const void* a, int n, int hw, int c, const float* scale, const float* shift, const float* wfc,
+                       int num_classes, const int32_t* target_cls, const float* logits, float* cam_lowres,
+                       int dtype, cudaStream_t s);
+cudaError_t launch_cam_upsample(const float* cam_lowres, int n, int side, int out_side, float* cam, cudaStream_t s);
+
+// layout helpers for the split (hook-protocol) API
+cudaError_t launch_nhwc_to_nchw_f32(const void* a_nhwc, int n, int hw, int c, float* out_nchw, int dtype,
+                                    cudaStream_t s);
+cudaError_t launch_head_from_nchw(const float* a_nchw, int n, int hw, int c, const float* scale, const float* shift,
+                                  float* pooled, cudaStream_t s);
+cudaError_t launch_head_backward(const float* a_nchw, const float* grad_logits, int n, int hw, int c,
+                                 const float* scale, const float* shift, const float* wfc, int num_classes,
+                                 float* grad_a, cudaStream_t s);
+cudaError_t launch_softmax_pack(const float* logits, const int64_t* labels, int n, int num_classes, float* packed,
+                                cudaStream_t s);
+
+}  // namespace b200df

@@ -1,0 +1,174 @@
+// Stem: 3x3 stride-2 pad-1 conv 3->32 (+folded BN bias, SiLU).
+// Replaces timm `conv_stem` + `bn1` at the head of the reference's
+// `model(images)` call (/root/reference/orchestration/orchestrator.py:590).
+//
+// Input is what the caller hands over: float32 NCHW (orchestrator.py:588), or -- for the
+// GPU-side input path -- uint8 HWC crops with ToTensor + Normalize
+// (orchestrator.py:340-345) fused into the load.  Output is NHWC (bf16 or fp32).
+//
+// HBM-bound by design intent (0.6 MB in + 0.8 MB out per image, 10.8 M MAC): the input patch is
+// staged once in shared memory (coalesced 128-bit row loads, zero halo), each thread produces two
+// adjacent output pixels x 32 channels from registers, weights are broadcast from shared memory.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200df {
+
+constexpr int kStemOC = 32;
+constexpr int kStemTR = 4;  // output rows per block
+constexpr int kStemThreads = 256;
+
+template <typename TOut, bool kU8>
+__global__ void __launch_bounds__(kStemThreads)
+stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict__ wgt,
+            const float* __restrict__ bias, TOut* __restrict__ out, float sc0, float sc1, float sc2,
+            float sh0, float sh1, float sh2) {
+  extern __shared__ float smem[];
+  const int Ho = H >> 1, Wo = W >> 1;
+  const int PW = W + 2;                  // patch width incl. left/right halo column
+  constexpr int PR = 2 * kStemTR + 1;    // patch rows
+  float* ws = smem;                      // [27][32]
+  float* bs = ws + 27 * kStemOC;         // [32]
+  float* patch = bs + kStemOC;           // [3][PR][PW]
+
+  const int n = blockIdx.y;
+  const int oh0 = blockIdx.x * kStemTR;
+  const int ih0 = 2 * oh0 - 1;
+  const int tid = threadIdx.x;
+
+  for (int i = tid; i < 27 * kStemOC; i += kStemThreads) {
+    int tap = i / kStemOC, oc = i % kStemOC;
+    ws[i] = wgt[oc * 27 + tap];
+  }
+  if (tid < kStemOC) bs[tid] = bias[tid];
+
+  // zero the halo columns
+  for (int i = tid; i < 3 * PR; i += kStemThreads) {
+    patch[i * PW] = 0.f;
+    patch[i * PW + PW - 1] = 0.f;
+  }
+  if constexpr (!kU8) {
+    const float* x = reinterpret_cast<const float*>(xin) + (size_t)n * 3 * H * W;
+    const int W4 = W >> 2;
+    for (int i = tid; i < 3 * PR * W4; i += kStemThreads) {
+      int q = i % W4, rc = i / W4;
+      int r = rc % PR, c = rc / PR;
+      int ih = ih0 + r;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ih >= 0 && ih < H) v = __ldg(reinterpret_cast<const float4*>(x + ((size_t)c * H + ih) * W) + q);
+      float* d = patch + (c * PR + r) * PW + 1 + 4 * q;
+      d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    }
+  } else {
+    const uint8_t* x = reinterpret_cast<const uint8_t*>(xin) + (size_t)n * H * W * 3;
+    const int RW = W * 3;  // bytes per row
+    const int RW4 = RW >> 2;
+    for (int i = tid; i < PR * RW4; i += kStemThreads) {
+      int q = i % RW4, r = i / RW4;
+      int ih = ih0 + r;
+      uint32_t v = 0;
+      bool ok = (ih >= 0 && ih < H);
+      if (ok) v = __ldg(reinterpret_cast<const uint32_t*>(x + (size_t)ih * RW) + q);
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        int e = 4 * q + b;
+        int col = e / 3, c = e - col * 3;
+        float f = (float)((v >> (8 * b)) & 0xffu);
+        float sc = c == 0 ? sc0 : (c == 1 ? sc1 : sc2);
+        float sh = c == 0 ? sh0 : (c == 1 ? sh1 : sh2);
+        patch[(c * PR + r) * PW + 1 + col] = ok ? fmaf(f, sc, sh) : 0.f;
+      }
+    }
+  }
+  __syncthreads();
+
+  const int pairs_per_row = (Wo + 1) >> 1;
+  const int npairs = kStemTR * pairs_per_row;
+  for (int p = tid; p < npairs; p += kStemThreads) {
+    const int r = p / pairs_per_row;
+    const int ow0 = (p - r * pairs_per_row) * 2;
+    const int oh = oh0 + r;
+    if (oh >= Ho) continue;
+    float acc0[kStemOC], acc1[kStemOC];
+#pragma unroll
+    for (int o = 0; o < kStemOC; ++o) { acc0[o] = bs[o]; acc1[o] = bs[o]; }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const float* prow = patch + (c * PR + 2 * r + ky) * PW + 2 * ow0;
+        float v[5];
+#pragma unroll
+        for (int i = 0; i < 5; ++i) v[i] = (2 * ow0 + i < PW) ? prow[i] : 0.f;
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          const float4* w4 = reinterpret_cast<const float4*>(ws + ((c * 3 + ky) * 3 + kx) * kStemOC);
+#pragma unroll
+          for (int o4 = 0; o4 < kStemOC / 4; ++o4) {
+            float4 w = w4[o4];
+            acc0[4 * o4 + 0] = fmaf(v[kx], w.x, acc0[4 * o4 + 0]);
+            acc0[4 * o4 + 1] = fmaf(v[kx], w.y, acc0[4 * o4 + 1]);
+            acc0[4 * o4 + 2] = fmaf(v[kx], w.z, acc0[4 * o4 + 2]);
+            acc0[4 * o4 + 3] = fmaf(v[kx], w.w, acc0[4 * o4 + 3]);
+            acc1[4 * o4 + 0] = fmaf(v[kx + 2], w.x, acc1[4 * o4 + 0]);
+            acc1[4 * o4 + 1] = fmaf(v[kx + 2], w.y, acc1[4 * o4 + 1]);
+            acc1[4 * o4 + 2] = fmaf(v[kx + 2], w.z, acc1[4 * o4 + 2]);
+            acc1[4 * o4 + 3] = fmaf(v[kx + 2], w.w, acc1[4 * o4 + 3]);
+          }
+        }
+      }
+    }
+    constexpr bool kFast = is_bf16<TOut>::value;
+    TOut* o0 = out + (((size_t)n * Ho + oh) * Wo + ow0) * kStemOC;
+#pragma unroll
+    for (int g = 0; g < kStemOC / 8; ++g) {
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = silu<kFast>(acc0[8 * g + j]);
+      store8<TOut>(o0 + 8 * g, f);
+    }
+    if (ow0 + 1 < Wo) {
+#pragma unroll
+      for (int g = 0; g < kStemOC / 8; ++g) {
+        float f[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = silu<kFast>(acc1[8 * g + j]);
+        store8<TOut>(o0 + kStemOC + 8 * g, f);
+      }
+    }
+  }
+}
+
+template <typename TOut, bool kU8>
+static cudaError_t stem_launch(const void* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
+                               float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  if ((w & 3) || (h & 1) || (w & 1)) return cudaErrorInvalidValue;
+  const int Ho = h / 2;
+  size_t smem = (27 * kStemOC + kStemOC + 3 * (2 * kStemTR + 1) * (w + 2)) * sizeof(float);
+  auto kern = stem_kernel<TOut, kU8>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  dim3 grid((Ho + kStemTR - 1) / kStemTR, n);
+  kern<<<grid, kStemThreads, smem, s>>>(x, h, w, wgt, bias, reinterpret_cast<TOut*>(out), sc0, sc1, sc2, sh0, sh1,
+                                        sh2);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_stem(const float* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
+                        int dtype, cudaStream_t s) {
+  if (dtype == kBF16) return stem_launch<bf16, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
+  return stem_launch<float, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
+}
+
+cudaError_t launch_stem_u8(const uint8_t* x, int n, int h, int w, const float* wgt, const float* bias, float sc0,
+                           float sc1, float sc2, float sh0, float sh1, float sh2, void* out, int dtype,
+                           cudaStream_t s) {
+  if (dtype == kBF16) return stem_launch<bf16, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
+  return stem_launch<float, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
+}
+
+}  // namespace b200df

@@ -1,0 +1,185 @@
+"""Python handle around one ``b200df_engine`` (C ABI in ``include/b200df.h``).
+
+PyTorch is used here only for device memory, streams and dtype bookkeeping; all
+arithmetic happens inside ``libb200df.so``.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import threading
+
+import torch
+
+from . import _lib
+
+_ALIGN = 1024
+
+
+def _ptr(t: torch.Tensor | None) -> C.c_void_p:
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream_ptr(device: torch.device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def require_cuda_f32(t: torch.Tensor, what: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(
+            f"{what} is on '{t.device}': the b200 backend has no CPU fallback -- put the model and "
+            "its inputs on a CUDA (sm_100) device (set `device: cuda` in the YAML)."
+        )
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{what} must be float32, got {t.dtype}")
+
+
+class Engine:
+    """One model instance on one GPU: weights (folded/packed) + a workspace per batch size."""
+
+    def __init__(self, arch: int, num_classes: int, device: torch.device) -> None:
+        self._lib = _lib.lib()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError(f"b200 backend needs a CUDA device, got '{device}' (no CPU fallback)")
+        index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", index)
+        self.num_classes = num_classes
+        self._h = C.c_void_p()
+        _lib.check(self._lib.b200df_create(arch, num_classes, index, C.byref(self._h)))
+        self.precision: int | None = None
+        self._ws: dict[int, tuple[torch.Tensor, int, int]] = {}
+        self._lock = threading.Lock()
+
+    # -- description ---------------------------------------------------------------------------------
+    def expected_tensors(self) -> list[tuple[str, int]]:
+        out = []
+        name = C.c_char_p()
+        numel = C.c_size_t()
+        for i in range(self._lib.b200df_num_tensors(self._h)):
+            _lib.check(self._lib.b200df_tensor_info(self._h, i, C.byref(name), C.byref(numel)))
+            out.append((name.value.decode(), int(numel.value)))
+        return out
+
+    # -- weights -------------------------------------------------------------------------------------
+    def load_state(self, state: dict[str, torch.Tensor], precision: int) -> None:
+        """Push every expected tensor (timm names) and fold/pack for ``precision``."""
+        with self._lock:
+            for name, numel in self.expected_tensors():
+                if name not in state:
+                    raise KeyError(f"state is missing '{name}'")
+                t = state[name].detach().to(device="cpu", dtype=torch.float32).contiguous()
+                if t.numel() != numel:
+                    raise ValueError(f"'{name}': {tuple(t.shape)} has {t.numel()} elements, engine expects {numel}")
+                _lib.check(self._lib.b200df_set_tensor(self._h, name.encode(), _ptr(t), numel, 0))
+            with torch.cuda.device(self.device):
+                _lib.check(self._lib.b200df_finalize(self._h, precision))
+            self.precision = precision
+            self._ws.clear()
+
+    # -- workspace -----------------------------------------------------------------------------------
+    def _workspace(self, n: int) -> tuple[int, int]:
+        hit = self._ws.get(n)
+        if hit is None:
+            need = C.c_size_t()
+            _lib.check(self._lib.b200df_workspace_bytes(self._h, n, 1, C.byref(need)))
+            buf = torch.empty(int(need.value) + _ALIGN, dtype=torch.uint8, device=self.device)
+            base = (buf.data_ptr() + _ALIGN - 1) // _ALIGN * _ALIGN
+            if len(self._ws) >= 4:  # keep a few batch sizes (full batch, ragged tail, n=1 from the UI)
+                self._ws.pop(next(iter(self._ws)))
+            hit = (buf, base, int(need.value))
+            self._ws[n] = hit
+        return hit[1], hit[2]
+
+    # -- hot path ------------------------------------------------------------------------------------
+    def forward(self, images: torch.Tensor) -> torch.Tensor:
+        require_cuda_f32(images, "images")
+        n = images.shape[0]
+        images = images.contiguous()
+        logits = torch.empty((n, self.num_classes), dtype=torch.float32, device=images.device)
+        if n == 0:
+            return logits
+        with self._lock, torch.cuda.device(images.device):
+            base, size = self._workspace(n)
+            _lib.check(self._lib.b200df_forward(self._h, _ptr(images), n, _ptr(logits), C.c_void_p(base), size,
+                                               _stream_ptr(images.device)))
+        return logits
+
+    def forward_u8(self, images_hwc: torch.Tensor, mean, std) -> torch.Tensor:
+        if not images_hwc.is_cuda or images_hwc.dtype != torch.uint8:
+            raise RuntimeError("forward_u8 expects a CUDA uint8 [n,224,224,3] tensor")
+        n = images_hwc.shape[0]
+        images_hwc = images_hwc.contiguous()
+        logits = torch.empty((n, self.num_classes), dtype=torch.float32, device=images_hwc.device)
+        if n == 0:
+            return logits
+        m = (C.c_float * 3)(*mean) if mean is not None else None
+        s = (C.c_float * 3)(*std) if std is not None else None
+        with self._lock, torch.cuda.device(images_hwc.device):
+            base, size = self._workspace(n)
+            _lib.check(self._lib.b200df_forward_u8(self._h, _ptr(images_hwc), n, m, s, _ptr(logits),
+                                                  C.c_void_p(base), size, _stream_ptr(images_hwc.device)))
+        return logits
+
+    def forward_cam(self, images: torch.Tensor, targets: torch.Tensor | None, want_map: bool = True):
+        """-> (logits [n,C], cam_lowres [n,7,7], cam [n,224,224] or None)."""
+        require_cuda_f32(images, "images")
+        n = images.shape[0]
+        images = images.contiguous()
+        dev = images.device
+        logits = torch.empty((n, self.num_classes), dtype=torch.float32, device=dev)
+        low = torch.empty((n, 7, 7), dtype=torch.float32, device=dev)
+        cam = torch.empty((n, images.shape[-2], images.shape[-1]), dtype=torch.float32, device=dev) if want_map else None
+        if n == 0:
+            return logits, low, cam
+        tgt = None
+        if targets is not None:
+            tgt = targets.to(device=dev, dtype=torch.int32).contiguous()
+        with self._lock, torch.cuda.device(dev):
+            base, size = self._workspace(n)
+            _lib.check(self._lib.b200df_forward_cam(self._h, _ptr(images), n, _ptr(tgt), _ptr(logits), _ptr(low),
+                                                   _ptr(cam), C.c_void_p(base), size, _stream_ptr(dev)))
+        return logits, low, cam
+
+    def trunk(self, images: torch.Tensor) -> torch.Tensor:
+        require_cuda_f32(images, "images")
+        n = images.shape[0]
+        images = images.contiguous()
+        a = torch.empty((n, 1280, 7, 7), dtype=torch.float32, device=images.device)
+        if n == 0:
+            return a
+        with self._lock, torch.cuda.device(images.device):
+            base, size = self._workspace(n)
+            _lib.check(self._lib.b200df_trunk(self._h, _ptr(images), n, _ptr(a), C.c_void_p(base), size,
+                                             _stream_ptr(images.device)))
+        return a
+
+    def head(self, a: torch.Tensor) -> torch.Tensor:
+        require_cuda_f32(a, "activation")
+        a = a.contiguous()
+        n = a.shape[0]
+        logits = torch.empty((n, self.num_classes), dtype=torch.float32, device=a.device)
+        with self._lock, torch.cuda.device(a.device):
+            _lib.check(self._lib.b200df_head(self._h, _ptr(a), n, _ptr(logits), _stream_ptr(a.device)))
+        return logits
+
+    def head_backward(self, a: torch.Tensor, grad_logits: torch.Tensor) -> torch.Tensor:
+        require_cuda_f32(a, "activation")
+        a = a.contiguous()
+        g = grad_logits.to(dtype=torch.float32).contiguous()
+        out = torch.empty_like(a)
+        with self._lock, torch.cuda.device(a.device):
+            _lib.check(self._lib.b200df_head_backward(self._h, _ptr(a), _ptr(g), a.shape[0], _ptr(out),
+                                                     _stream_ptr(a.device)))
+        return out
+
+    def close(self) -> None:
+        if self._h:
+            self._lib.b200df_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self) -> None:  # noqa: D105
+        try:
+            self.close()
+        except Exception:  # pragma: no cover - interpreter teardown
+            pass

@@ -1,0 +1,172 @@
+/*
+ * b200df.h -- C ABI of libb200df.so: the B200-native (sm_100a) engine for the
+ * DeepfakeDetection eval hot path (batched backbone forward + Grad-CAM).
+ *
+ * Plain pointers and sizes only; no torch types.  All device pointers are raw
+ * CUDA device addresses on the device the handle was created for; `stream` is a
+ * cudaStream_t (CUstream) passed as void*.  Every call returns 0 on success or a
+ * negative B200DF_E_* code; b200df_last_error() returns a thread-local message.
+ * Nothing in here ever computes on the CPU: if no sm_100 device is present the
+ * compute entry points fail with B200DF_E_NO_DEVICE (there is no fallback).
+ *
+ * What each entry point replaces in the reference (thourihan/DeepfakeDetection):
+ *   b200df_create / set_tensor / finalize
+ *        <- spec.builder(name, num_classes) + model.to(device) + model.eval() +
+ *           model.load_state_dict(state, strict=False)
+ *           (orchestration/model_registry.py:32-47, orchestration/orchestrator.py:350-377)
+ *   b200df_forward
+ *        <- `logits = model(images)` in the eval loops
+ *           (orchestration/orchestrator.py:526-532 and :587-592; web_ui.py:266-268)
+ *   b200df_forward_cam / b200df_cam
+ *        <- GradCAM(model, [target_layer])(input_tensor, [ClassifierOutputTarget(c)])
+ *           (web_ui.py:96-114 target rule, web_ui.py:275-279 call)
+ *   b200df_head / b200df_head_backward
+ *        <- the autograd leg pytorch-grad-cam drives through hooks on `_conv_head`
+ *           (web_ui.py:108-114)
+ *   b200df_softmax_pack
+ *        <- probs = softmax(logits, 1); preds = argmax(probs, 1)
+ *           (orchestration/orchestrator.py:591-592), packed for the all-gather
+ */
+#ifndef B200DF_H_
+#define B200DF_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+#define B200DF_ABI_VERSION 1
+
+/* status codes */
+#define B200DF_OK 0
+#define B200DF_E_INVALID (-1)   /* bad argument / unknown tensor name / wrong shape */
+#define B200DF_E_STATE (-2)     /* call out of order (e.g. forward before finalize)  */
+#define B200DF_E_CUDA (-3)      /* a CUDA runtime/driver call failed                  */
+#define B200DF_E_NO_DEVICE (-4) /* no sm_100 device: there is no CPU fallback         */
+#define B200DF_E_WORKSPACE (-5) /* workspace too small or misaligned                  */
+
+/* architectures */
+#define B200DF_ARCH_EFFICIENTNET_B0 0
+
+/* precisions (b200df_finalize) */
+#define B200DF_PREC_BF16 0 /* bf16 NHWC activations/weights, fp32 accumulate, tcgen05 GEMMs */
+#define B200DF_PREC_FP32 1 /* fp32 NHWC activations/weights, fp32 FFMA everywhere (strict)  */
+
+typedef struct b200df_engine* b200df_handle;
+
+const char* b200df_last_error(void);
+int b200df_abi_version(void);
+
+/* Number of CUDA devices with compute capability 10.x visible to this process (0 if none). */
+int b200df_device_count(void);
+
+/* ---- lifecycle ------------------------------------------------------------------------- */
+int b200df_create(int arch, int num_classes, int device, b200df_handle* out);
+int b200df_destroy(b200df_handle h);
+
+/* Provide one fp32 tensor of the timm state_dict by name ("conv_stem.weight",
+ * "blocks.3.1.bn2.running_var", ...).  `data` is host memory unless is_device != 0.
+ * `numel` must match the architecture's shape for that name.  Unknown names return
+ * B200DF_E_INVALID (the Python loader mirrors strict=False by skipping them loudly). */
+int b200df_set_tensor(b200df_handle h, const char* name, const float* data, size_t numel, int is_device);
+
+/* Number of tensors the architecture expects / name+numel of the i-th one. */
+int b200df_num_tensors(b200df_handle h);
+int b200df_tensor_info(b200df_handle h, int index, const char** name, size_t* numel);
+
+/* Fold BN into conv weights (fp32, on the host), convert to `precision`, lay out for the
+ * kernels and upload.  May be called again after further set_tensor calls. */
+int b200df_finalize(b200df_handle h, int precision);
+
+/* ---- the hot path ---------------------------------------------------------------------- */
+/* Bytes of device scratch needed for a batch of n images (mode: 0 = forward, 1 = forward+CAM). */
+int b200df_workspace_bytes(b200df_handle h, int n, int mode, size_t* bytes);
+
+/* images: float32 [n,3,224,224] NCHW contiguous (the reference's call convention,
+ * orchestrator.py:588-590); logits: float32 [n,num_classes].  Asynchronous on `stream`. */
+int b200df_forward(b200df_handle h, const float* images, int n, float* logits,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* Same forward, input given as uint8 [n,224,224,3] HWC crops; ToTensor (/255) and
+ * Normalize(mean,std) (orchestrator.py:340-345) are fused into the stem.  mean/std: 3 floats
+ * each (host), or NULL for "val_normalize: false". */
+int b200df_forward_u8(b200df_handle h, const uint8_t* images_hwc, int n, const float* mean,
+                      const float* stdv, float* logits, void* workspace, size_t workspace_bytes,
+                      void* stream);
+
+/* Forward + Grad-CAM in one pass.  target_cls: int32 [n] device (NULL = argmax of logits).
+ * cam_lowres: float32 [n,7,7] (ReLU'd, unnormalised) or NULL; cam: float32 [n,224,224]
+ * in [0,1] (min-max, bilinear upsample, min-max) or NULL. */
+int b200df_forward_cam(b200df_handle h, const float* images, int n, const int32_t* target_cls,
+                       float* logits, float* cam_lowres, float* cam, void* workspace,
+                       size_t workspace_bytes, void* stream);
+
+/* Split form used by the autograd/hook protocol: trunk -> A (raw conv_head output,
+ * float32 [n,1280,7,7] NCHW as a hook on `_conv_head` would see it), head: A -> logits,
+ * head_backward: dL/dA given dL/dlogits. */
+int b200df_trunk(b200df_handle h, const float* images, int n, float* a_nchw, void* workspace,
+                 size_t workspace_bytes, void* stream);
+int b200df_head(b200df_handle h, const float* a_nchw, int n, float* logits, void* stream);
+int b200df_head_backward(b200df_handle h, const float* a_nchw, const float* grad_logits, int n,
+                         float* grad_a_nchw, void* stream);
+
+/* softmax + argmax of [n,num_classes] logits packed as records {p[0..C), pred, label} of
+ * (C+2) floats per image -- the buffer the multi-GPU harness all-gathers. labels may be NULL. */
+int b200df_softmax_pack(const float* logits, const int64_t* labels, int n, int num_classes,
+                        float* packed, void* stream);
+
+/* Count of kernel launches issued by this library on the calling thread since the last
+ * reset (bench.py reports it as gpu_launches). */
+long long b200df_launch_count(void);
+void b200df_reset_launch_count(void);
+
+/* ---- per-kernel entry points (unit tests, ncu) ------------------------------------------ */
+/* dtype: 0 = bf16, 1 = fp32 for activations/weights; all layouts NHWC; bias fp32. */
+
+/* Stem: fp32 NCHW [n,3,H,W] -> act [n,H/2,W/2,32]; w: [32,27] fp32 (BN folded), bias [32]; SiLU. */
+int b200df_k_stem(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias,
+                  void* out, int dtype, void* stream);
+
+/* Depthwise kxk (k=3|5, stride 1|2, pad (k-1)/2) + bias + SiLU; optional fp32 pooled sums
+ * pool[n,c] += sum_hw(out) (must be zeroed by the caller).  wgt: [k*k, c] fp32 (tap-major). */
+int b200df_k_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
+                    const float* bias, void* out, float* pool, int dtype, void* stream);
+
+/* Squeeze-excite MLP on pooled sums: gate[n,c] = sigmoid(W2 silu(W1 (pool*inv_hw) + b1) + b2).
+ * w1: conv_reduce [rd,c]; w2t: conv_expand TRANSPOSED to [rd,c]. */
+int b200df_k_se(const float* pool, int n, int c, int rd, float inv_hw, const float* w1,
+                const float* b1, const float* w2t, const float* b2, float* gate, void* stream);
+
+/* Pointwise (1x1) conv as GEMM: out[m, cout] = act( (x[m,:] * gate[m / rows_per_img, :]) . w^T + bias )
+ * (+ residual).  x: [m,cin]; w: [cout,cin] in `dtype`; gate fp32 [m/rows_per_img, cin] or NULL;
+ * residual [m,cout] or NULL; act: 0 none, 1 SiLU.  impl: 0 = tcgen05 (bf16 only), 1 = SIMT. */
+int b200df_k_pwconv(const void* x, long long m, int cin, int cout, const void* wgt, const float* bias,
+                    const float* gate, int rows_per_img, const void* residual, int act, void* out,
+                    int dtype, int impl, void* stream);
+
+/* Head pooling: pooled[n,c] = mean_hw silu(a[n,hw,c]*scale[c] + shift[c]); a in `dtype` NHWC. */
+int b200df_k_head_pool(const void* a, int n, int hw, int c, const float* scale, const float* shift,
+                       float* pooled, int dtype, void* stream);
+
+/* Fused Grad-CAM on the raw conv_head output a [n,hw,c] (dtype): closed-form channel weights
+ * (BN -> SiLU -> mean -> Linear), weighted sum, ReLU -> cam_lowres [n,hw] fp32. */
+int b200df_k_cam(const void* a, int n, int hw, int c, const float* scale, const float* shift,
+                 const float* wfc, int num_classes, const int32_t* target_cls, float* cam_lowres,
+                 int dtype, void* stream);
+
+/* min-max -> bilinear (half-pixel, edge clamp) upsample to out_hw x out_hw -> relu -> min-max. */
+int b200df_k_cam_upsample(const float* cam_lowres, int n, int side, int out_side, float* cam,
+                          void* stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DF_H_ */

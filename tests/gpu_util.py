@@ -1,0 +1,51 @@
+"""Thin torch-tensor wrappers over the per-kernel C-ABI entry points (GPU tests only)."""
+
+import ctypes as C
+
+import torch
+
+from deepfakedetection_b200 import _lib
+
+
+def P(t):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def tdtype(dt):
+    return torch.bfloat16 if dt == _lib.DT_BF16 else torch.float32
+
+
+def k_stem(x, w, b, dt):
+    n, _, h, wd = x.shape
+    out = torch.empty((n, h // 2, wd // 2, 32), dtype=tdtype(dt), device=x.device)
+    _lib.check(_lib.lib().b200df_k_stem(P(x), n, h, wd, P(w), P(b), P(out), dt, stream()))
+    return out
+
+
+def k_dwconv(x, w_tap_major, bias, k, stride, dt, pool=True):
+    n, h, wd, c = x.shape
+    pad = (k - 1) // 2
+    ho, wo = (h + 2 * pad - k) // stride + 1, (wd + 2 * pad - k) // stride + 1
+    out = torch.empty((n, ho, wo, c), dtype=tdtype(dt), device=x.device)
+    pl = torch.zeros((n, c), dtype=torch.float32, device=x.device) if pool else None
+    _lib.check(_lib.lib().b200df_k_dwconv(P(x), n, h, wd, c, k, stride, P(w_tap_major), P(bias), P(out), P(pl), dt, stream()))
+    return out, pl
+
+
+def k_se(pool, inv_hw, w1, b1, w2t, b2):
+    n, c = pool.shape
+    gate = torch.empty_like(pool)
+    _lib.check(_lib.lib().b200df_k_se(P(pool), n, c, w1.shape[0], C.c_float(inv_hw), P(w1), P(b1), P(w2t), P(b2), P(gate), stream()))
+    return gate
+
+
+def k_pwconv(x, w, bias, gate=None, rows_per_img=1, residual=None, act=0, dt=_lib.DT_BF16, impl=0):
+    m, cin = x.shape
+    cout = w.shape[0]
+    out = torch.empty((m, cout), dtype=tdtype(dt), device=x.device)
+    _lib.check(_lib.lib().b200df_k_pwconv(P(x), m, cin, cout, P(w), P(bias), P(gate), rows_per_img, P(residual), act, P(out), dt, impl, stream()))
+    return out

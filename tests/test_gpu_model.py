@@ -1,0 +1,196 @@
+"""End-to-end parity on a B200: the registered backend module (nn.Module -> torch.library op ->
+C ABI -> CUDA) vs the fp32 oracle on identical synthetic inputs and weights.
+
+Tolerances are BASELINE.json's: fp32 path max |dlogit| <= 1e-3; bf16 path max |dsoftmax| <= 2e-2
+with >= 99.9 % argmax agreement; Grad-CAM cosine >= 0.99 after normalisation."""
+
+import numpy as np
+import pytest
+import torch
+
+from deepfakedetection_b200 import _lib, registry
+from deepfakedetection_b200.gradcam import ClassifierOutputTarget, GradCAM
+
+pytestmark = pytest.mark.gpu
+
+TOL_FP32_LOGIT = 1e-3
+TOL_BF16_SOFTMAX = 2e-2
+MIN_ARGMAX_AGREE = 0.999
+MIN_CAM_COSINE = 0.99
+
+
+@pytest.fixture(autouse=True)
+def _need_gpu():
+    assert torch.cuda.is_available() and _lib.lib().b200df_device_count() > 0, "these tests need a B200"
+    torch.cuda.set_device(0)
+
+
+def build(oracle_model, name):
+    """The reference's load_model sequence (orchestrator.py:356-375)."""
+    spec = registry.get_model_spec(name)
+    model = spec.builder(name, 2)
+    model.to(torch.device("cuda"))
+    model.eval()
+    model.load_state_dict(oracle_model.state_dict(), strict=False)
+    return model
+
+
+@pytest.fixture(scope="module")
+def model_fp32(oracle_model):
+    return build(oracle_model, "efficientnet_b0.b200_fp32")
+
+
+@pytest.fixture(scope="module")
+def model_bf16(oracle_model):
+    return build(oracle_model, "efficientnet_b0")
+
+
+@pytest.fixture(scope="module")
+def batch(oracle_model):
+    from oracle.effnet_b0 import synth_images
+
+    x = synth_images(64, seed=11)
+    with torch.no_grad():
+        ref = oracle_model(x)
+    return x, ref
+
+
+def test_fp32_path_logits(model_fp32, batch):
+    x, ref = batch
+    with torch.inference_mode():
+        out = model_fp32(x.cuda())
+    assert out.shape == ref.shape and out.dtype == torch.float32 and out.is_cuda
+    err = (out.cpu() - ref).abs().max().item()
+    assert err <= TOL_FP32_LOGIT, f"max |dlogit| = {err}"
+
+
+def test_bf16_path_softmax_and_argmax(model_bf16, batch):
+    x, ref = batch
+    with torch.inference_mode():
+        out = model_bf16(x.cuda()).cpu()
+    dp = (torch.softmax(out, 1) - torch.softmax(ref, 1)).abs().max().item()
+    assert dp <= TOL_BF16_SOFTMAX, f"max |dsoftmax| = {dp}"
+    # argmax agreement, ignoring images whose oracle margin is below the softmax tolerance
+    margin = (ref[:, 0] - ref[:, 1]).abs()
+    decided = margin > 0.1
+    agree = (out.argmax(1) == ref.argmax(1))[decided].float().mean().item()
+    assert agree >= MIN_ARGMAX_AGREE, f"argmax agreement {agree}"
+
+
+def test_bf16_simt_gemm_agrees_with_tcgen05(oracle_model, model_bf16, batch, monkeypatch):
+    """Same bf16 network with the CUDA-core GEMM swapped in: isolates the tcgen05 kernel."""
+    x, _ = batch
+    monkeypatch.setenv("B200DF_GEMM", "simt")
+    simt = build(oracle_model, "efficientnet_b0")
+    with torch.inference_mode():
+        a = simt(x[:16].cuda()).cpu()
+    monkeypatch.delenv("B200DF_GEMM")
+    with torch.inference_mode():
+        b = model_bf16(x[:16].cuda()).cpu()
+    assert (a - b).abs().max().item() < 0.15
+
+
+def test_golden_vectors(model_fp32, golden):
+    from oracle.effnet_b0 import synth_images
+
+    x = synth_images(4, seed=123).cuda()
+    logits, low, cam = model_fp32.forward_cam(x, torch.from_numpy(golden["targets"]))
+    np.testing.assert_allclose(logits.cpu().numpy(), golden["logits"], atol=3e-3)
+    np.testing.assert_allclose(low.cpu().numpy(), golden["cam_low"], atol=1e-3 * max(1.0, float(golden["cam_low"].max())))
+    np.testing.assert_allclose(cam[:, ::8, ::8].cpu().numpy(), golden["cam_ds"], atol=5e-3)
+
+
+@pytest.mark.parametrize("n", [1, 3, 37, 130])
+def test_ragged_batches_and_batch_invariance(model_fp32, model_bf16, batch, n):
+    """Last batch is ragged (orchestrator.py:587) and the UI sends n=1 (web_ui.py:251-264): any n
+    must work and a sample's logits must not depend on its batch."""
+    x, ref = batch
+    xs = x.repeat(3, 1, 1, 1)[:n].cuda()
+    refs = ref.repeat(3, 1)[:n]
+    with torch.inference_mode():
+        out32 = model_fp32(xs).cpu()
+        out16 = model_bf16(xs).cpu()
+        full16 = model_bf16(x.cuda()).cpu().repeat(3, 1)[:n]
+    assert (out32 - refs).abs().max().item() <= TOL_FP32_LOGIT
+    assert (out16 - full16).abs().max().item() <= 1e-5, "bf16 logits changed with the batch size"
+
+
+def test_empty_batch(model_bf16):
+    with torch.inference_mode():
+        out = model_bf16(torch.empty(0, 3, 224, 224, device="cuda"))
+    assert out.shape == (0, 2)
+
+
+def test_u8_input_path_matches_float_path(model_fp32):
+    """GPU-side ToTensor + Normalize (orchestrator.py:340-345) fused into the stem."""
+    g = torch.Generator().manual_seed(3)
+    u8 = torch.randint(0, 256, (5, 224, 224, 3), generator=g, dtype=torch.uint8)
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    x = (u8.float() / 255 - torch.tensor(mean)) / torch.tensor(std)
+    x = x.permute(0, 3, 1, 2).contiguous()
+    with torch.inference_mode():
+        a = model_fp32(x.cuda()).cpu()
+        b = model_fp32.forward_u8(u8.cuda(), mean, std).cpu()
+    assert (a - b).abs().max().item() < 5e-3 * max(1.0, a.abs().max().item())
+
+
+def _cos(a, b):
+    a, b = a.flatten(1).double(), b.flatten(1).double()
+    return torch.nn.functional.cosine_similarity(a, b, dim=1)
+
+
+@pytest.mark.parametrize("which", ["fp32", "bf16"])
+def test_fused_gradcam_cosine(which, model_fp32, model_bf16, oracle_model, batch):
+    from oracle.gradcam import gradcam_autograd
+
+    model = model_fp32 if which == "fp32" else model_bf16
+    x, ref = batch
+    x = x[:16]
+    targets = ref[:16].argmax(1)
+    _, low_ref, cam_ref = gradcam_autograd(oracle_model, x, targets)
+    logits, low, cam = model.forward_cam(x.cuda(), targets)
+    keep = low_ref.flatten(1).max(1).values > 1e-6  # an all-zero map has no direction
+    assert _cos(cam.cpu(), cam_ref)[keep].min().item() >= MIN_CAM_COSINE
+    assert _cos(low.cpu(), low_ref)[keep].min().item() >= MIN_CAM_COSINE
+    assert float(cam.min()) >= 0.0 and float(cam.max()) <= 1.0 + 1e-6
+    # default target = argmax of the engine's own logits
+    _, low2, _ = model.forward_cam(x.cuda(), None)
+    same = logits.argmax(1).cpu() == targets
+    assert torch.allclose(low2.cpu()[same], low.cpu()[same], atol=1e-6)
+
+
+def test_gradcam_hook_protocol_like_web_ui(model_fp32, oracle_model, batch):
+    """web_ui.py:96-114 + 275-279: target = model._conv_head; GradCAM(...)(input_tensor, targets)[0]."""
+    from oracle.gradcam import gradcam_autograd
+
+    x, ref = batch
+    one = x[:1]
+    cls_idx = int(ref[:1].argmax(1))
+    target_layer = getattr(model_fp32, "_conv_head")
+    _, _, cam_ref = gradcam_autograd(oracle_model, one, torch.tensor([cls_idx]))
+    for use_hooks in (False, True):
+        with GradCAM(model=model_fp32, target_layers=[target_layer], use_hooks=use_hooks) as cam:
+            gray = cam(input_tensor=one.cuda(), targets=[ClassifierOutputTarget(cls_idx)])[0]
+        assert gray.shape == (224, 224) and gray.dtype == np.float32
+        assert _cos(torch.from_numpy(gray)[None], cam_ref).item() >= MIN_CAM_COSINE, f"use_hooks={use_hooks}"
+
+
+def test_reload_state_dict_repacks(model_fp32, oracle_model, batch):
+    x, ref = batch
+    sd = {k: v.clone() for k, v in oracle_model.state_dict().items()}
+    sd["classifier.bias"] = sd["classifier.bias"] + 1.0
+    model_fp32.load_state_dict(sd, strict=False)
+    with torch.inference_mode():
+        out = model_fp32(x[:4].cuda()).cpu()
+    assert (out - (ref[:4] + 1.0)).abs().max().item() <= TOL_FP32_LOGIT
+    model_fp32.load_state_dict(oracle_model.state_dict(), strict=False)
+
+
+def test_sharded_evaluation_single_rank(model_bf16, batch):
+    from deepfakedetection_b200.evaluate import evaluate_sharded
+
+    x, ref = batch
+    labels = ref.argmax(1)
+    res = evaluate_sharded(model_bf16, x, labels, batch_size=24)
+    assert res["probs"].shape == (64, 2) and res["accuracy"] >= 0.95
+    assert np.array(res["confusion_matrix"]).sum() == 64
