@@ -45,6 +45,10 @@ SIGNATURES: dict[str, tuple] = {
     "b200df_softmax_pack": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "b200df_launch_count": (_ll, []),
     "b200df_reset_launch_count": (None, []),
+    "b200df_set_profile": (_i, [_vp, _i]),
+    "b200df_profile_count": (_i, [_vp]),
+    "b200df_profile_get": (_i, [_vp, _i, C.POINTER(C.c_char_p), C.POINTER(_f), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "b200df_profile_reset": (_i, [_vp]),
     "b200df_k_stem": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "b200df_k_dwconv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp]),
     "b200df_k_se": (_i, [_vp, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp]),

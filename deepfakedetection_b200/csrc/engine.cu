@@ -169,6 +169,10 @@ extern "C" int b200df_destroy(b200df_handle h) {
   cudaGetDevice(&prev);
   cudaSetDevice(h->device);
   free_device(h);
+  for (auto& r : h->prof) {
+    if (r.e0) cudaEventDestroy(r.e0);
+    if (r.e1) cudaEventDestroy(r.e1);
+  }
   cudaSetDevice(prev);
   delete h;
   return B200DF_OK;
@@ -433,6 +437,27 @@ extern "C" int b200df_workspace_bytes(b200df_handle h, int n, int mode, size_t* 
 // ---- forward schedule ---------------------------------------------------------------------------------------
 namespace {
 
+// Profiling: when h->profile is set, every launch of the schedule is bracketed by two CUDA events
+// on the launching stream and tagged with its algorithmic bytes / flops.
+ProfRec* prof_begin(b200df_engine* h, cudaStream_t s, const char* cls, int layer, double bytes, double flops) {
+  if (!h->profile) return nullptr;
+  if (h->prof_used == h->prof.size()) {
+    ProfRec r;
+    if (cudaEventCreate(&r.e0) != cudaSuccess || cudaEventCreate(&r.e1) != cudaSuccess) return nullptr;
+    h->prof.push_back(r);
+  }
+  ProfRec* r = &h->prof[h->prof_used++];
+  if (layer >= 0) snprintf(r->name, sizeof(r->name), "%s.%d", cls, layer);
+  else snprintf(r->name, sizeof(r->name), "%s", cls);
+  r->bytes = bytes;
+  r->flops = flops;
+  cudaEventRecord(r->e0, s);
+  return r;
+}
+void prof_end(ProfRec* r, cudaStream_t s) {
+  if (r) cudaEventRecord(r->e1, s);
+}
+
 struct GemmCall {  // one pointwise conv in schedule order
   const PwLayer* L;
   const void* x;
@@ -490,37 +515,60 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
   CU_OK(cudaMemsetAsync(pool, 0, h->pool_floats_per_img * n * sizeof(float), s));
   void* cur = ws + W.t0;
   void* nxt = ws + W.t1;
+  const double es = h->precision == B200DF_PREC_BF16 ? 2.0 : 4.0;
+  const double ho0 = h->img / 2;
+  ProfRec* pr = prof_begin(h, s, "stem", -1,
+                           (double)n * (3.0 * h->img * h->img * (in_kind == kInF32NCHW ? 4.0 : 1.0) + ho0 * ho0 * 32 * es),
+                           2.0 * n * ho0 * ho0 * 32 * 27);
   if (in_kind == kInF32NCHW) {
     CU_OK(launch_stem(reinterpret_cast<const float*>(images), n, h->img, h->img, h->stem_w, h->stem_b, cur, dt, s));
   } else {
     CU_OK(launch_stem_u8(reinterpret_cast<const uint8_t*>(images), n, h->img, h->img, h->stem_w, h->stem_b, in_sc[0],
                          in_sc[1], in_sc[2], in_sh[0], in_sh[1], in_sh[2], cur, dt, s));
   }
+  prof_end(pr, s);
   int gi = 0;
   for (size_t i = 0; i < h->blocks.size(); ++i) {
     const BlockCfg& b = h->blocks[i];
     const BlockDev& d = h->bdev[i];
     const long long m_in = (long long)n * b.hin * b.hin, m_out = (long long)n * b.hout * b.hout;
     const void* dw_in = cur;
+    const int li = (int)i;
     if (b.expand) {
+      pr = prof_begin(h, s, "expand", li, (double)m_in * (b.cin + b.mid) * es + (double)b.mid * b.cin * es,
+                      2.0 * m_in * b.cin * b.mid);
       GemmCall g{&d.expand, cur, m_in, nullptr, 1, nullptr, 1, ws + W.e};
       int rc = run_gemm(h, g, gi++, s);
       if (rc) return rc;
+      prof_end(pr, s);
       dw_in = ws + W.e;
     }
     float* pool_b = pool + d.pool_off * n;
     float* gate_b = gate + d.pool_off * n;
+    pr = prof_begin(h, s, "dw", li, ((double)m_in + (double)m_out) * b.mid * es, 2.0 * m_out * b.mid * b.k * b.k);
     CU_OK(launch_dwconv(dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b, dt, s));
+    prof_end(pr, s);
+    pr = prof_begin(h, s, "se", li, (double)n * b.mid * 8.0 + 2.0 * b.mid * b.rd * 4.0, 4.0 * n * b.mid * b.rd);
     CU_OK(launch_se(pool_b, n, b.mid, b.rd, 1.0f / (float)(b.hout * b.hout), d.se_w1, d.se_b1, d.se_w2t, d.se_b2,
                     gate_b, s));
+    prof_end(pr, s);
+    pr = prof_begin(h, s, "project", li,
+                    (double)m_out * (b.mid + b.cout * (b.skip ? 2 : 1)) * es + (double)b.mid * b.cout * es,
+                    2.0 * m_out * b.mid * b.cout);
     GemmCall g{&d.project, ws + W.d, m_out, gate_b, b.hout * b.hout, b.skip ? cur : nullptr, 0, nxt};
     int rc = run_gemm(h, g, gi++, s);
     if (rc) return rc;
+    prof_end(pr, s);
     std::swap(cur, nxt);
   }
   const int hw = h->blocks.back().hout * h->blocks.back().hout;
+  const int cin_head = h->blocks.back().cout;
+  pr = prof_begin(h, s, "conv_head", -1, (double)n * hw * (cin_head + 1280) * es + 1280.0 * cin_head * es,
+                  2.0 * n * hw * cin_head * 1280);
   GemmCall g{&h->head, cur, (long long)n * hw, nullptr, 1, nullptr, 0, ws + W.a};
-  return run_gemm(h, g, gi++, s);
+  int rc = run_gemm(h, g, gi++, s);
+  prof_end(pr, s);
+  return rc;
 }
 
 int check_call(b200df_engine* h, int n, const void* ws, size_t ws_bytes, Workspace* W) {
@@ -541,8 +589,14 @@ int run_head(b200df_engine* h, int n, uint8_t* ws, const Workspace& W, float* lo
   const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
   const int hw = h->blocks.back().hout * h->blocks.back().hout;
   float* pooled = reinterpret_cast<float*>(ws + W.pooled);
+  const double es = h->precision == B200DF_PREC_BF16 ? 2.0 : 4.0;
+  ProfRec* pr = prof_begin(h, s, "head_pool", -1, (double)n * hw * 1280 * es + (double)n * 1280 * 4, 8.0 * n * hw * 1280);
   CU_OK(launch_head_pool(ws + W.a, n, hw, 1280, h->head_scale, h->head_shift, pooled, dt, s));
+  prof_end(pr, s);
+  pr = prof_begin(h, s, "classifier", -1, (double)n * 1280 * 4 + (double)n * h->num_classes * 4,
+                  2.0 * n * 1280 * h->num_classes);
   CU_OK(launch_classifier(pooled, n, 1280, h->fc_w, h->fc_b, h->num_classes, logits, s));
+  prof_end(pr, s);
   return B200DF_OK;
 }
 
@@ -598,9 +652,16 @@ extern "C" int b200df_forward_cam(b200df_handle h, const float* images, int n, c
   rc = run_head(h, n, ws, W, lg, s);
   if (rc) return rc;
   float* low = cam_lowres ? cam_lowres : reinterpret_cast<float*>(ws + W.cam_low);
+  const double es = dt == kBF16 ? 2.0 : 4.0;
+  ProfRec* pr = prof_begin(h, s, "cam", -1, (double)n * hw * 1280 * es + (double)n * hw * 4, 12.0 * n * hw * 1280);
   CU_OK(launch_cam(ws + W.a, n, hw, 1280, h->head_scale, h->head_shift, h->fc_w, h->num_classes, target_cls, lg, low,
                    dt, s));
-  if (cam) CU_OK(launch_cam_upsample(low, n, side, h->img, cam, s));
+  prof_end(pr, s);
+  if (cam) {
+    pr = prof_begin(h, s, "cam_upsample", -1, (double)n * (hw + (double)h->img * h->img) * 4, 8.0 * n * h->img * h->img);
+    CU_OK(launch_cam_upsample(low, n, side, h->img, cam, s));
+    prof_end(pr, s);
+  }
   return B200DF_OK;
 }
 
@@ -668,6 +729,36 @@ extern "C" int b200df_softmax_pack(const float* logits, const int64_t* labels, i
                                    void* stream) {
   if (n < 0 || num_classes < 1 || (n > 0 && (!logits || !packed))) return fail(B200DF_E_INVALID, "bad argument");
   CU_OK(launch_softmax_pack(logits, labels, n, num_classes, packed, reinterpret_cast<cudaStream_t>(stream)));
+  return B200DF_OK;
+}
+
+// ---- profiling (bench.py's per-kernel roofline; never enabled inside a timed region) ---------------------------
+extern "C" int b200df_set_profile(b200df_handle h, int enable) {
+  if (!h) return fail(B200DF_E_INVALID, "NULL handle");
+  h->profile = enable != 0;
+  h->prof_used = 0;
+  return B200DF_OK;
+}
+
+extern "C" int b200df_profile_count(b200df_handle h) { return h ? (int)h->prof_used : 0; }
+
+extern "C" int b200df_profile_get(b200df_handle h, int index, const char** name, float* ms, double* bytes,
+                                  double* flops) {
+  if (!h || index < 0 || index >= (int)h->prof_used) return fail(B200DF_E_INVALID, "profile index out of range");
+  ProfRec& r = h->prof[index];
+  CU_OK(cudaEventSynchronize(r.e1));
+  float t = 0.f;
+  CU_OK(cudaEventElapsedTime(&t, r.e0, r.e1));
+  if (name) *name = r.name;
+  if (ms) *ms = t;
+  if (bytes) *bytes = r.bytes;
+  if (flops) *flops = r.flops;
+  return B200DF_OK;
+}
+
+extern "C" int b200df_profile_reset(b200df_handle h) {
+  if (!h) return fail(B200DF_E_INVALID, "NULL handle");
+  h->prof_used = 0;
   return B200DF_OK;
 }
 

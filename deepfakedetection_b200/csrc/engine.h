@@ -52,6 +52,14 @@ struct Plan {  // cached tensor maps for one (n, workspace) pair
   std::vector<TcGemmArgs> gemms;  // in schedule order
 };
 
+// Per-launch profiling record (b200df_set_profile): CUDA events around one kernel launch plus
+// the ALGORITHMIC bytes / flops of that launch.
+struct ProfRec {
+  char name[48];
+  double bytes = 0, flops = 0;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+};
+
 struct Workspace {
   size_t t0, t1, e, d, a, pool, gate, pooled, logits, cam_low, total;
 };
@@ -79,4 +87,8 @@ struct b200df_engine {
   size_t pool_floats_per_img = 0;
   int gemm_impl = 0;  // 0 = tcgen05 (bf16), 1 = SIMT
   b200df::Plan plan;
+  // profiling (off by default; never on inside a timed region)
+  bool profile = false;
+  std::vector<b200df::ProfRec> prof;   // event pool, reused across passes
+  size_t prof_used = 0;
 };

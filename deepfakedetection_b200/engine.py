@@ -173,6 +173,20 @@ class Engine:
                                                      _stream_ptr(a.device)))
         return out
 
+    # -- per-launch profiling (bench.py) -----------------------------------------------------------------
+    def set_profile(self, enable: bool) -> None:
+        _lib.check(self._lib.b200df_set_profile(self._h, 1 if enable else 0))
+
+    def profile_records(self) -> list[tuple[str, float, float, float]]:
+        """[(name, ms, algorithmic bytes, flops)] for every launch since the last reset (synchronises)."""
+        out = []
+        name, ms, by, fl = C.c_char_p(), C.c_float(), C.c_double(), C.c_double()
+        for i in range(self._lib.b200df_profile_count(self._h)):
+            _lib.check(self._lib.b200df_profile_get(self._h, i, C.byref(name), C.byref(ms), C.byref(by), C.byref(fl)))
+            out.append((name.value.decode(), float(ms.value), float(by.value), float(fl.value)))
+        _lib.check(self._lib.b200df_profile_reset(self._h))
+        return out
+
     def close(self) -> None:
         if self._h:
             self._lib.b200df_destroy(self._h)

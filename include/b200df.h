@@ -125,6 +125,17 @@ int b200df_softmax_pack(const float* logits, const int64_t* labels, int n, int n
 long long b200df_launch_count(void);
 void b200df_reset_launch_count(void);
 
+/* ---- per-launch profiling (bench.py's per-kernel roofline) -------------------------------- */
+/* When enabled, every kernel launch of forward / forward_cam is bracketed by two CUDA events on
+ * the launching stream and tagged "<class>[.<block>]" with its ALGORITHMIC bytes and flops
+ * (DESIGN.md section 4).  Records accumulate until b200df_profile_reset; read them after a
+ * stream synchronize.  Keep it off inside timed regions. */
+int b200df_set_profile(b200df_handle h, int enable);
+int b200df_profile_count(b200df_handle h);
+int b200df_profile_get(b200df_handle h, int index, const char** name, float* ms, double* bytes,
+                       double* flops);
+int b200df_profile_reset(b200df_handle h);
+
 /* ---- per-kernel entry points (unit tests, ncu) ------------------------------------------ */
 /* dtype: 0 = bf16, 1 = fp32 for activations/weights; all layouts NHWC; bias fp32. */
 
