@@ -149,7 +149,11 @@ cudaError_t launch_dwconv(const void* x, int n, int h, int w, int c, int k, int 
                           const float* bias, void* out, float* pool, int dtype, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   if (c % 8 != 0 || c > 12288) return cudaErrorInvalidValue;
-  if (dtype == kBF16) return dw_dispatch<bf16>(x, n, h, w, c, k, stride, wgt, bias, out, pool, s);
+  if (dtype == kBF16) {
+    DwPlan plan;  // bf16: TMA-staged kernel (dwconv_tma.cu) whenever the shape allows it
+    if (plan_dwconv_tma(plan, x, n, h, w, c, k, stride, wgt, bias, out, pool) == 0) return launch_dwconv_tma(plan, s);
+    return dw_dispatch<bf16>(x, n, h, w, c, k, stride, wgt, bias, out, pool, s);
+  }
   return dw_dispatch<float>(x, n, h, w, c, k, stride, wgt, bias, out, pool, s);
 }
 

@@ -1,0 +1,438 @@
+// Depthwise kxk conv (k = 3|5, stride 1|2, pad (k-1)/2) + folded-BN bias + SiLU + SE pool sums,
+// bf16 NHWC, for sm_100a: TMA halo staging + register-resident weights + sliding accumulators.
+// Replaces timm `conv_dw` + `bn1/bn2`(+SiLU) and the `se` mean_hw, the
+// depthwise leg of every MBConv inside the reference's `model(images)`
+// (/root/reference/orchestration/orchestrator.py:590).
+//
+// Shape of the problem: 12.2 MB of HBM traffic and 34.5 M MAC per image over 16 layers -- HBM-bound,
+// but only if the instruction stream stays near 25-40 issue slots per output element, so:
+//   * a CTA owns (image, 32-channel block, OTW x OTH output tile); the input tile INCLUDING its halo
+//     arrives with ONE cp.async.bulk.tensor (TMA) per tile: out-of-image halo pixels and channels
+//     past C are zero-filled by the TMA unit, so the compute loop has no bounds checks at all.
+//     Stride-2 layers use a 5-D tensor map that splits columns into (pair, parity), which lands even
+//     and odd input columns in separate contiguous planes -> bank-conflict-free reads at stride 2;
+//   * a thread owns 2 channels x 1 output column x TH output rows; the k*k*2 folded weights live in
+//     registers for the whole tile; input rows stream through once (k LDS.32 per row) and every loaded
+//     value feeds up to k*k FMAs on the TH sliding fp32 accumulators;
+//   * 16 lanes cover one pixel's 32 channels (64 B), the two half-warps take adjacent columns, so each
+//     warp-wide LDS.32 reads 128 contiguous bytes and each store writes two full 64-B segments;
+//   * tiles are double-buffered: the TMA for tile i+1 is in flight while tile i is computed;
+//   * SE pooling: per-thread sums -> shuffle -> shared atomics -> one global atomic per (tile, channel).
+#include "common.cuh"
+#include "kernels.h"
+#include "tc.cuh"
+
+#include <algorithm>
+
+namespace b200df {
+
+using namespace tc;
+
+constexpr int kDwCB = 32;       // channels per CTA tile (64 B of every pixel)
+constexpr int kDwMaxGroup = 8;  // images per tile for the small-spatial layers
+
+
+// ---- packed fp32x2 helpers (sm_100: FFMA2 / FADD2 / FMUL2 -- two fp32 lanes per issue slot) ----
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// two bf16 channels (one 32-bit word) -> packed fp32 pair
+__device__ __forceinline__ f32x2 bf16x2_to_f32x2(uint32_t raw) {
+  return pack2(__uint_as_float(raw << 16), __uint_as_float(raw & 0xffff0000u));
+}
+
+struct DwTile { int cb, tx, ty, ng; };
+
+template <int K, int S, int TH>
+__global__ void __launch_bounds__(256)
+dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-align by OFFSET (not by pointer round-trip) so the compiler keeps the shared address space -> LDS
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  __shared__ uint64_t full_bar[2];
+  __shared__ float spool[2][kDwMaxGroup][kDwCB];
+
+  constexpr int PAD = (K - 1) / 2;
+  constexpr int PADE = (S == 2) ? 2 : PAD;   // stride 2: the box starts on an even column
+  constexpr int XOFF = PADE - PAD;           // extra left columns inside the box
+  constexpr int RIN = (TH - 1) * S + K;      // input rows one strip touches
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+  const int cp = lane & 15;   // channel pair inside the 32-channel block
+  const int xs = lane >> 4;   // which of the warp's two adjacent output columns
+  const int ngroups = (p.n + p.gimg - 1) / p.gimg;
+  const int total = p.tiles_x * p.tiles_y * p.ncb * ngroups;
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tmap);
+    mbar_init(&full_bar[0], 1);
+    mbar_init(&full_bar[1], 1);
+    fence_barrier_init();
+  }
+  for (int i = tid; i < 2 * kDwMaxGroup * kDwCB; i += blockDim.x) (&spool[0][0][0])[i] = 0.f;
+  __syncthreads();
+
+  // tile index -> (cb fastest, then tile x, tile y, image group): neighbouring CTAs read the same pixels'
+  // other channel blocks at the same time (full DRAM lines, halos shared through L2).  Decoded once,
+  // then advanced by gridDim.x in mixed radix (no divisions in the tile loop).
+  auto decode = [&](int t) {
+    DwTile d;
+    d.cb = t % p.ncb;
+    int r = t / p.ncb;
+    d.tx = r % p.tiles_x;
+    r /= p.tiles_x;
+    d.ty = r % p.tiles_y;
+    d.ng = r / p.tiles_y;
+    return d;
+  };
+  const DwTile step = decode((int)gridDim.x);
+  auto advance = [&](DwTile d) {
+    d.cb += step.cb;
+    int c = d.cb >= p.ncb;
+    d.cb -= c ? p.ncb : 0;
+    d.tx += step.tx + c;
+    c = d.tx >= p.tiles_x;
+    d.tx -= c ? p.tiles_x : 0;
+    d.ty += step.ty + c;
+    c = d.ty >= p.tiles_y;
+    d.ty -= c ? p.tiles_y : 0;
+    d.ng += step.ng + c;
+    return d;
+  };
+  auto issue = [&](const DwTile& d, int stage) {
+    mbar_arrive_expect_tx(&full_bar[stage], p.box_bytes);
+    uint8_t* dst = smem + stage * p.stage_stride;
+    if constexpr (S == 1) {
+      tma_load_4d(dst, &tmap, d.cb * kDwCB, d.tx * p.otw - PAD, d.ty * p.oth - PAD, d.ng * p.gimg, &full_bar[stage]);
+    } else {
+      // dims: (c, column pair, column parity, row, image)
+      tma_load_5d(dst, &tmap, d.cb * kDwCB, d.tx * p.otw - PADE / 2, 0, d.ty * p.oth * 2 - PAD, d.ng * p.gimg,
+                  &full_bar[stage]);
+    }
+  };
+
+  DwTile cur = decode((int)blockIdx.x);
+  if (tid == 0 && (int)blockIdx.x < total) issue(cur, 0);
+
+  const int col_pairs = p.otw >> 1;
+  const int per_img = col_pairs * (p.oth / TH);
+  const int items = per_img * p.gimg;
+  const int row_bytes = (S == 1) ? p.bw * 64 : p.bw * 128;  // S=2: two parity planes of bw pairs per row
+  const size_t out_row = (size_t)p.Wo * p.C;                // elements between output rows
+
+  // folded weights + bias for this thread's channel pair, pre-scaled by 1/2 so the accumulators hold
+  // h = x/2 directly (silu(x) = h + h*tanh(h)).  When gridDim.x is a multiple of ncb (the planner
+  // arranges that) every tile of this CTA has the same channel block and they are loaded once.
+  int c0 = cur.cb * kDwCB + cp * 2;
+  bool c_ok = c0 < p.C;
+  f32x2 w[K * K];
+  f32x2 bias2 = 0ull;
+  auto load_weights = [&]() {
+    const f32x2 half2 = pack2(0.5f, 0.5f);
+#pragma unroll
+    for (int i = 0; i < K * K; ++i) {
+      float2 v = c_ok ? __ldg(reinterpret_cast<const float2*>(p.wgt + (size_t)i * p.C + c0)) : make_float2(0.f, 0.f);
+      w[i] = mul2(pack2(v.x, v.y), half2);
+    }
+    float2 bb = c_ok ? __ldg(reinterpret_cast<const float2*>(p.bias + c0)) : make_float2(0.f, 0.f);
+    bias2 = mul2(pack2(bb.x, bb.y), half2);
+  };
+  load_weights();
+
+  int it = 0;
+  for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+    const int stage = it & 1;
+    const DwTile nxt = advance(cur);
+    if (tid == 0 && t + (int)gridDim.x < total) issue(nxt, stage ^ 1);
+
+    if (!p.cb_fixed) {  // cb changes from tile to tile: reload this channel pair's weights
+      c0 = cur.cb * kDwCB + cp * 2;
+      c_ok = c0 < p.C;
+      load_weights();
+    }
+
+    mbar_wait(&full_bar[stage], (uint32_t)((it >> 1) & 1));
+    const uint8_t* tile = smem + stage * p.stage_stride;
+
+    for (int item = warp; item < items; item += nwarps) {
+      const int g = (item * p.inv_per_img) >> 16;           // image inside the group
+      const int rem = item - g * per_img;
+      const int st = (rem * p.inv_cp) >> 16;                // row strip
+      const int x = (rem - st * col_pairs) * 2 + xs;        // output column inside the tile
+      const int y0 = st * TH;                               // first output row inside the tile
+      f32x2 acc[TH];
+#pragma unroll
+      for (int j = 0; j < TH; ++j) acc[j] = bias2;
+
+      // (input row 0 of the strip, this thread's first column, its channel pair)
+      const uint8_t* base = tile + (g * p.img_bytes + y0 * S * row_bytes + x * 64 + cp * 4);
+#pragma unroll
+      for (int rr = 0; rr < RIN; ++rr) {
+        f32x2 v[K];
+#pragma unroll
+        for (int kx = 0; kx < K; ++kx) {
+          uint32_t raw;
+          if constexpr (S == 1) {
+            raw = *reinterpret_cast<const uint32_t*>(base + rr * row_bytes + kx * 64);
+          } else {
+            const int ic = kx + XOFF;  // column offset inside the box relative to 2*x
+            raw = *reinterpret_cast<const uint32_t*>(base + rr * row_bytes + (ic & 1) * (p.bw * 64) + (ic >> 1) * 64);
+          }
+          v[kx] = bf16x2_to_f32x2(raw);
+        }
+#pragma unroll
+        for (int ky = 0; ky < K; ++ky) {
+          // input row rr feeds output row (rr - ky) / S when that is an integer in [0, TH)
+          if ((rr - ky) >= 0 && (rr - ky) % S == 0 && (rr - ky) / S < TH) {
+            const int j = (rr - ky) / S;
+#pragma unroll
+            for (int kx = 0; kx < K; ++kx) acc[j] = fma2(v[kx], w[ky * K + kx], acc[j]);
+          }
+        }
+      }
+      // epilogue: SiLU (h + h*tanh h), bf16 pack, store, pool partials
+      const int ox = cur.tx * p.otw + x;
+      const int oy0 = cur.ty * p.oth + y0;
+      const int img = cur.ng * p.gimg + g;
+      f32x2 ps = 0ull;
+      if (c_ok && ox < p.Wo && img < p.n) {
+        bf16* op = reinterpret_cast<bf16*>(p.out) + (((size_t)img * p.Ho + oy0) * p.Wo + ox) * p.C + c0;
+        const bool rows_full = oy0 + TH <= p.Ho;
+#pragma unroll
+        for (int j = 0; j < TH; ++j) {
+          float h0, h1;
+          unpack2(acc[j], h0, h1);
+          const f32x2 f = fma2(acc[j], pack2(tanh_fast(h0), tanh_fast(h1)), acc[j]);
+          float f0, f1;
+          unpack2(f, f0, f1);
+          if (rows_full || oy0 + j < p.Ho) {
+            *reinterpret_cast<uint32_t*>(op) = pack_bf16x2(f0, f1);
+            ps = add2(ps, f);
+          }
+          op += out_row;
+        }
+      }
+      if (p.pool != nullptr) {
+        float s0, s1;
+        unpack2(ps, s0, s1);
+        s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+        if (xs == 0) {
+          atomicAdd(&spool[stage][g][cp * 2], s0);
+          atomicAdd(&spool[stage][g][cp * 2 + 1], s1);
+        }
+      }
+    }
+    __syncthreads();  // everyone is done with smem stage `stage`; spool[stage] is complete
+    if (p.pool != nullptr) {
+      for (int i = tid; i < p.gimg * kDwCB; i += blockDim.x) {
+        const int g = i >> 5, cc = i & 31;
+        const float v = spool[stage][g][cc];
+        spool[stage][g][cc] = 0.f;
+        const int c = cur.cb * kDwCB + cc;
+        const int img = cur.ng * p.gimg + g;
+        if (c < p.C && img < p.n) atomicAdd(p.pool + (size_t)img * p.C + c, v);
+      }
+    }
+    cur = nxt;
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------------
+
+typedef CUresult (*PFN_encodeTiledNd)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsigned long long* dims,
+                        const unsigned long long* strides_bytes, const unsigned* box, int swizzle) {
+  static PFN_encodeTiledNd enc = nullptr;
+  if (!enc) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return -1;
+    enc = reinterpret_cast<PFN_encodeTiledNd>(fn);
+  }
+  if (rank < 2 || rank > 5 || (reinterpret_cast<uintptr_t>(base) & 15)) return -2;
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+    if (i > 0) {
+      gstr[i - 1] = strides_bytes[i];
+      if (strides_bytes[i] % 16) return -2;
+    }
+  }
+  CUtensorMapSwizzle sw = swizzle == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                          : swizzle == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                          : swizzle == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
+                                          : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = enc(reinterpret_cast<CUtensorMap*>(tmap_out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
+                   const_cast<void*>(base), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
+namespace {
+
+template <int K, int S, int TH>
+cudaError_t dw_tma_launch(const DwPlan& pl, cudaStream_t s) {
+  auto kern = dwconv_tma_kernel<K, S, TH>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  kern<<<pl.grid, pl.block, pl.smem, s>>>(*reinterpret_cast<const CUtensorMap*>(pl.tmap), pl.p);
+  count_launch();
+  return cudaGetLastError();
+}
+
+template <int K, int S, int TH>
+int dw_tma_occupancy(int block, size_t smem) {
+  auto kern = dwconv_tma_kernel<K, S, TH>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) return 1;
+  int nb = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, block, smem) != cudaSuccess || nb < 1) nb = 1;
+  return nb;
+}
+
+int dw_tma_occupancy_dispatch(int k, int stride, int th, int block, size_t smem) {
+#define DW_OCC(K_, S_, TH_) \
+  if (k == K_ && stride == S_ && th == TH_) return dw_tma_occupancy<K_, S_, TH_>(block, smem)
+  DW_OCC(3, 1, 8); DW_OCC(3, 1, 7); DW_OCC(3, 2, 8); DW_OCC(3, 2, 7);
+  DW_OCC(5, 1, 8); DW_OCC(5, 1, 7); DW_OCC(5, 2, 8); DW_OCC(5, 2, 7);
+#undef DW_OCC
+  return 1;
+}
+
+constexpr size_t kDwBoxLimit = 54 * 1024;  // bytes per stage: 2 stages x <= 54 KB -> 2 CTAs per SM
+
+}  // namespace
+
+int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
+                    const float* bias, void* out, float* pool) {
+  if (n <= 0 || c % 8 || (k != 3 && k != 5) || (stride != 1 && stride != 2)) return -1;
+  if (stride == 2 && (w & 1)) return -1;
+  const int pad = (k - 1) / 2;
+  const int Ho = (h + 2 * pad - k) / stride + 1, Wo = (w + 2 * pad - k) / stride + 1;
+  const int th = (Ho % 8 == 0) ? 8 : 7;
+  const int strips_total = (Ho + th - 1) / th;
+  // choose the output tile: even width wasting at most one column, height a multiple of TH dividing the
+  // strip count; maximise useful/loaded pixels subject to the per-stage smem limit, prefer >= 8 warp items
+  double best_score = -1.0;
+  int b_otw = 0, b_m = 0, b_bw = 0, b_bh = 0, b_g = 1;
+  for (int otw = 2; otw <= 32; otw += 2) {
+    const int tiles_x = (Wo + otw - 1) / otw;
+    if (tiles_x * otw - Wo > 1) continue;
+    for (int m = 1; m <= strips_total; ++m) {
+      if (strips_total % m) continue;
+      const int oth = m * th;
+      int bw, bh = (oth - 1) * stride + k;
+      size_t bytes;
+      if (stride == 1) {
+        bw = otw + k - 1;
+        bytes = (size_t)bw * bh * 64;
+      } else {
+        const int cols = (otw - 1) * 2 + k + (2 - pad);  // incl. the even-start offset
+        bw = (cols + 1) / 2;                              // column pairs
+        bytes = (size_t)bw * 2 * bh * 64;
+      }
+      if (bw > 256 || bh > 256) continue;
+      const bool whole = tiles_x == 1 && m == strips_total;  // the tile is the whole image
+      for (int g = 1; g <= (whole ? kDwMaxGroup : 1); g *= 2) {
+        if (g > n && g > 1) break;
+        if (bytes * g > kDwBoxLimit) break;
+        const int items = (otw / 2) * m * g;
+        double eff = (double)std::min(otw, Wo) * std::min(oth, Ho) * stride * stride / ((double)bytes / 64.0);
+        double score = eff * std::min(1.0, 0.5 + items / 32.0);
+        if (score > best_score) {
+          best_score = score;
+          b_otw = otw; b_m = m; b_bw = bw; b_bh = bh; b_g = g;
+        }
+      }
+    }
+  }
+  if (best_score < 0) return -1;
+  DwTmaParams& p = plan.p;
+  p.C = c; p.Ho = Ho; p.Wo = Wo;
+  p.otw = b_otw; p.oth = b_m * th;
+  p.tiles_x = (Wo + b_otw - 1) / b_otw;
+  p.tiles_y = strips_total / b_m;
+  p.ncb = (c + kDwCB - 1) / kDwCB;
+  p.n = n;
+  p.bw = b_bw; p.bh = b_bh;
+  p.gimg = b_g;
+  p.img_bytes = (int)((stride == 1 ? (size_t)b_bw : (size_t)b_bw * 2) * b_bh * 64);
+  p.inv_cp = (65536 + b_otw / 2 - 1) / (b_otw / 2);
+  p.inv_per_img = (65536 + (b_otw / 2) * b_m - 1) / ((b_otw / 2) * b_m);
+  p.box_bytes = (uint32_t)p.img_bytes * (uint32_t)b_g;
+  p.stage_stride = (int)((p.box_bytes + 1023) & ~1023u);
+  p.wgt = wgt; p.bias = bias; p.out = out; p.pool = pool;
+  int rc;
+  if (stride == 1) {
+    unsigned long long dims[4] = {(unsigned long long)c, (unsigned long long)w, (unsigned long long)h, (unsigned long long)n};
+    unsigned long long str[4] = {2, (unsigned long long)c * 2, (unsigned long long)w * c * 2, (unsigned long long)h * w * c * 2};
+    unsigned box[4] = {kDwCB, (unsigned)b_bw, (unsigned)b_bh, (unsigned)b_g};
+    rc = encode_tmap_nd_bf16(plan.tmap, x, 4, dims, str, box, 0);
+  } else {
+    unsigned long long dims[5] = {(unsigned long long)c, (unsigned long long)(w / 2), 2, (unsigned long long)h, (unsigned long long)n};
+    unsigned long long str[5] = {2, (unsigned long long)c * 4, (unsigned long long)c * 2, (unsigned long long)w * c * 2,
+                                 (unsigned long long)h * w * c * 2};
+    unsigned box[5] = {kDwCB, (unsigned)b_bw, 2, (unsigned)b_bh, (unsigned)b_g};
+    rc = encode_tmap_nd_bf16(plan.tmap, x, 5, dims, str, box, 0);
+  }
+  if (rc) return rc;
+  plan.k = k; plan.stride = stride; plan.th = th;
+  const int items = (b_otw / 2) * b_m * b_g;
+  plan.block = items >= 8 ? 256 : (items >= 4 ? 128 : 64);
+  plan.smem = 1024 + 2 * (size_t)p.stage_stride;
+  const long long total = (long long)p.tiles_x * p.tiles_y * p.ncb * ((n + b_g - 1) / b_g);
+  const int per_sm = dw_tma_occupancy_dispatch(k, stride, th, plan.block, plan.smem);
+  long long grid = std::min<long long>(total, (long long)kNumSMs * per_sm);
+  p.cb_fixed = 0;
+  if (grid >= p.ncb) {  // a grid that is a multiple of ncb keeps every CTA on one channel block
+    grid = grid / p.ncb * p.ncb;
+    p.cb_fixed = 1;
+  }
+  plan.grid = (int)grid;
+  plan.x = x;
+  return 0;
+}
+
+cudaError_t launch_dwconv_tma(const DwPlan& pl, cudaStream_t s) {
+#define DW_CASE(K_, S_, TH_) \
+  if (pl.k == K_ && pl.stride == S_ && pl.th == TH_) return dw_tma_launch<K_, S_, TH_>(pl, s)
+  DW_CASE(3, 1, 8); DW_CASE(3, 1, 7); DW_CASE(3, 2, 8); DW_CASE(3, 2, 7);
+  DW_CASE(5, 1, 8); DW_CASE(5, 1, 7); DW_CASE(5, 2, 8); DW_CASE(5, 2, 7);
+#undef DW_CASE
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace b200df

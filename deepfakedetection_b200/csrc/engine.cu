@@ -546,7 +546,24 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
     float* pool_b = pool + d.pool_off * n;
     float* gate_b = gate + d.pool_off * n;
     pr = prof_begin(h, s, "dw", li, ((double)m_in + (double)m_out) * b.mid * es, 2.0 * m_out * b.mid * b.k * b.k);
-    CU_OK(launch_dwconv(dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b, dt, s));
+    {
+      bool done = false;
+      if (dt == kBF16) {
+        if (h->plan.dws.size() != h->blocks.size()) h->plan.dws.assign(h->blocks.size(), DwPlan());
+        DwPlan& dp = h->plan.dws[i];
+        if (dp.x != dw_in || dp.p.n != n || dp.p.pool != pool_b) {
+          dp.x = nullptr;
+          if (plan_dwconv_tma(dp, dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b) != 0)
+            dp.x = nullptr;
+        }
+        if (dp.x != nullptr) {
+          CU_OK(launch_dwconv_tma(dp, s));
+          done = true;
+        }
+      }
+      if (!done)
+        CU_OK(launch_dwconv(dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b, dt, s));
+    }
     prof_end(pr, s);
     pr = prof_begin(h, s, "se", li, (double)n * b.mid * 8.0 + 2.0 * b.mid * b.rd * 4.0, 4.0 * n * b.mid * b.rd);
     CU_OK(launch_se(pool_b, n, b.mid, b.rd, 1.0f / (float)(b.hout * b.hout), d.se_w1, d.se_b1, d.se_w2t, d.se_b2,

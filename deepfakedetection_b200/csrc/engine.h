@@ -50,6 +50,7 @@ struct Plan {  // cached tensor maps for one (n, workspace) pair
   int n = -1;
   void* ws = nullptr;
   std::vector<TcGemmArgs> gemms;  // in schedule order
+  std::vector<DwPlan> dws;        // per block (bf16 path); x == nullptr -> not planned yet
 };
 
 // Per-launch profiling record (b200df_set_profile): CUDA events around one kernel launch plus

@@ -24,6 +24,41 @@ cudaError_t launch_stem_u8(const uint8_t* x_hwc, int n, int h, int w, const floa
 cudaError_t launch_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
                           const float* bias, void* out, float* pool, int dtype, cudaStream_t s);
 
+struct DwTmaParams {
+  int C, Ho, Wo;
+  int otw, oth;          // output tile (otw even, oth multiple of TH)
+  int tiles_x, tiles_y, ncb, n;
+  int bw;                // box width in pixels (S=1) or column PAIRS (S=2)
+  int bh;                // box height in input rows
+  int cb_fixed;          // gridDim.x % ncb == 0: a CTA's tiles all share one channel block
+  int gimg;              // images per tile (the box spans gimg images; small-spatial layers)
+  int img_bytes;         // bytes of one image's box inside a stage
+  int inv_cp, inv_per_img;  // ceil(65536 / col_pairs), ceil(65536 / (col_pairs * strips))
+  uint32_t box_bytes;
+  int stage_stride;      // bytes between the two smem stages (1024-aligned)
+  const float* wgt;      // [k*k, C] fp32, BN folded
+  const float* bias;     // [C]
+  void* out;               // [n, Ho, Wo, C]
+  float* pool;           // [n, C] or nullptr
+};
+
+// A planned depthwise launch: tensor map + tile geometry for one (layer, n, buffers) combination.
+struct DwPlan {
+  alignas(64) unsigned char tmap[128];
+  DwTmaParams p;
+  int k = 0, stride = 0, th = 0;
+  int grid = 0, block = 0;
+  size_t smem = 0;
+  const void* x = nullptr;  // cache key
+};
+// bf16 only.  Returns 0 on success (plan filled), <0 if this shape is not supported by the TMA kernel.
+int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
+                    const float* bias, void* out, float* pool);
+cudaError_t launch_dwconv_tma(const DwPlan& plan, cudaStream_t s);
+// Generic N-d bf16 tensor map (dims/strides innermost first; strides[0] is implicit).  0 on success.
+int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsigned long long* dims,
+                        const unsigned long long* strides_bytes, const unsigned* box, int swizzle);
+
 cudaError_t launch_se(const float* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
                       const float* w2, const float* b2, float* gate, cudaStream_t s);
 

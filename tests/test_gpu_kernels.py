@@ -58,8 +58,9 @@ def test_dwconv(c, h, k, s, dt):
     ref = F.silu(F.conv2d(x.float().permute(0, 3, 1, 2), w, b, stride=s, padding=(k - 1) // 2, groups=c))
     out, pool = k_dwconv(x, w.reshape(c, k * k).t().contiguous(), b, k, s, dt)
     torch.testing.assert_close(out.float(), ref.permute(0, 2, 3, 1), **tol(dt))
-    # pool sums must be of what the consumer reads (the stored, possibly bf16-rounded, values)
-    torch.testing.assert_close(pool, out.float().sum((1, 2)), atol=2e-2 if dt == BF else 2e-3, rtol=1e-3)
+    # SE pool sums: the reference pools the fp32 activation (timm `se` mean_hw), so compare with the
+    # fp32 reference sum (fast-tanh SiLU on the bf16 path: ~1e-3 relative per element)
+    torch.testing.assert_close(pool, ref.sum((2, 3)), atol=5e-2 if dt == BF else 2e-3, rtol=2e-3 if dt == BF else 1e-4)
 
 
 @pytest.mark.parametrize("c,rd", [(32, 8), (96, 4), (144, 6), (240, 10), (480, 20), (672, 28), (1152, 48)])
