@@ -97,6 +97,18 @@ __device__ __forceinline__ void store8<float>(float* __restrict__ p, const float
 template <typename T> struct is_bf16 { static constexpr bool value = false; };
 template <> struct is_bf16<bf16> { static constexpr bool value = true; };
 
+// ---- deterministic pooled sums ----------------------------------------------------------------
+// SE pool sums are accumulated across CTAs with 64-bit INTEGER atomics on a Q24 fixed-point value
+// (resolution 2^-24, range +-2^39): integer addition is associative, so the result does not depend on
+// the order in which tiles retire and a forward pass is bit-reproducible run to run.
+typedef long long pool_t;
+constexpr float kPoolScale = 16777216.0f;         // 2^24
+constexpr float kPoolInvScale = 1.0f / 16777216.0f;
+__device__ __forceinline__ void pool_add(pool_t* dst, float v) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)__float2ll_rn(v * kPoolScale));
+}
+__device__ __forceinline__ float pool_value(pool_t v) { return (float)((double)v * (double)kPoolInvScale); }
+
 // ---- warp reductions ----------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

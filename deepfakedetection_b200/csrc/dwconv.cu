@@ -7,7 +7,8 @@
 // HBM-bound: each thread owns 8 channels (one 128-bit vector) of a 1 x TW output strip and slides the
 // k x (TW*s + k - s) input window through registers, so every input vector is loaded once per
 // thread and re-used by up to k taps; neighbouring strips hit L1.  Accumulation is fp32.
-// Pool sums: shared-memory atomics per block, one global atomic per (block, channel).
+// Pool sums: Q24 fixed-point integer atomics (shared per block, then one global atomic per (block, channel)),
+// so the sums are independent of scheduling order (bit-reproducible).
 #include "common.cuh"
 #include "kernels.h"
 
@@ -18,8 +19,8 @@ constexpr int kDwThreads = 256;
 template <typename T, int K, int S, int TW>
 __global__ void __launch_bounds__(kDwThreads)
 dwconv_kernel(const T* __restrict__ x, T* __restrict__ out, const float* __restrict__ wgt,
-              const float* __restrict__ bias, float* __restrict__ pool, int H, int W, int C, int Ho, int Wo) {
-  extern __shared__ float spool[];  // [C]
+              const float* __restrict__ bias, pool_t* __restrict__ pool, int H, int W, int C, int Ho, int Wo) {
+  extern __shared__ unsigned long long spool[];  // [C] Q24
   constexpr int PAD = (K - 1) / 2;
   constexpr int IW = (TW - 1) * S + K;  // input columns a strip touches
   constexpr bool kFast = is_bf16<T>::value;
@@ -29,7 +30,7 @@ dwconv_kernel(const T* __restrict__ x, T* __restrict__ out, const float* __restr
   const int total = Ho * WT * CG;
   const bool do_pool = pool != nullptr;
   if (do_pool) {
-    for (int i = threadIdx.x; i < C; i += kDwThreads) spool[i] = 0.f;
+    for (int i = threadIdx.x; i < C; i += kDwThreads) spool[i] = 0ull;
     __syncthreads();
   }
   const T* xn = x + (size_t)n * H * W * C;
@@ -107,18 +108,19 @@ dwconv_kernel(const T* __restrict__ x, T* __restrict__ out, const float* __restr
     }
     if (do_pool) {
 #pragma unroll
-      for (int e = 0; e < 8; ++e) atomicAdd(&spool[c0 + e], psum[e]);
+      for (int e = 0; e < 8; ++e) atomicAdd(&spool[c0 + e], (unsigned long long)__float2ll_rn(psum[e] * kPoolScale));
     }
   }
   if (do_pool) {
     __syncthreads();
-    for (int i = threadIdx.x; i < C; i += kDwThreads) atomicAdd(&pool[(size_t)n * C + i], spool[i]);
+    for (int i = threadIdx.x; i < C; i += kDwThreads)
+      atomicAdd(reinterpret_cast<unsigned long long*>(pool) + (size_t)n * C + i, spool[i]);
   }
 }
 
 template <typename T, int K, int S, int TW>
 static cudaError_t dw_launch(const void* x, int n, int h, int w, int c, const float* wgt, const float* bias, void* out,
-                             float* pool, cudaStream_t s) {
+                             pool_t* pool, cudaStream_t s) {
   constexpr int PAD = (K - 1) / 2;
   const int Ho = (h + 2 * PAD - K) / S + 1, Wo = (w + 2 * PAD - K) / S + 1;
   const int WT = (Wo + TW - 1) / TW;
@@ -129,7 +131,7 @@ static cudaError_t dw_launch(const void* x, int n, int h, int w, int c, const fl
   if (max_bx < 1) max_bx = 1;
   if (bx > max_bx) bx = max_bx;
   dim3 grid(bx, n);
-  dwconv_kernel<T, K, S, TW><<<grid, kDwThreads, c * sizeof(float), s>>>(
+  dwconv_kernel<T, K, S, TW><<<grid, kDwThreads, c * sizeof(unsigned long long), s>>>(
       reinterpret_cast<const T*>(x), reinterpret_cast<T*>(out), wgt, bias, pool, h, w, c, Ho, Wo);
   count_launch();
   return cudaGetLastError();
@@ -137,7 +139,7 @@ static cudaError_t dw_launch(const void* x, int n, int h, int w, int c, const fl
 
 template <typename T>
 static cudaError_t dw_dispatch(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                               const float* bias, void* out, float* pool, cudaStream_t s) {
+                               const float* bias, void* out, pool_t* pool, cudaStream_t s) {
   if (k == 3 && stride == 1) return dw_launch<T, 3, 1, 4>(x, n, h, w, c, wgt, bias, out, pool, s);
   if (k == 3 && stride == 2) return dw_launch<T, 3, 2, 2>(x, n, h, w, c, wgt, bias, out, pool, s);
   if (k == 5 && stride == 1) return dw_launch<T, 5, 1, 4>(x, n, h, w, c, wgt, bias, out, pool, s);
@@ -146,9 +148,9 @@ static cudaError_t dw_dispatch(const void* x, int n, int h, int w, int c, int k,
 }
 
 cudaError_t launch_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                          const float* bias, void* out, float* pool, int dtype, cudaStream_t s) {
+                          const float* bias, void* out, pool_t* pool, int dtype, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
-  if (c % 8 != 0 || c > 12288) return cudaErrorInvalidValue;
+  if (c % 8 != 0 || c > 6144) return cudaErrorInvalidValue;
   if (dtype == kBF16) {
     DwPlan plan;  // bf16: TMA-staged kernel (dwconv_tma.cu) whenever the shape allows it
     if (plan_dwconv_tma(plan, x, n, h, w, c, k, stride, wgt, bias, out, pool) == 0) return launch_dwconv_tma(plan, s);

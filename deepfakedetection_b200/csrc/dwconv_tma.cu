@@ -17,7 +17,9 @@
 //   * 16 lanes cover one pixel's 32 channels (64 B), the two half-warps take adjacent columns, so each
 //     warp-wide LDS.32 reads 128 contiguous bytes and each store writes two full 64-B segments;
 //   * tiles are double-buffered: the TMA for tile i+1 is in flight while tile i is computed;
-//   * SE pooling: per-thread sums -> shuffle -> shared atomics -> one global atomic per (tile, channel).
+//   * SE pooling, order-independent (bit-reproducible): per-thread sums -> shuffle -> a shared slot owned by
+//     one thread per (warp, image, channel) -> fixed-order sum over warps -> ONE Q24 fixed-point integer
+//     atomic per (tile, channel) in global memory.
 #include "common.cuh"
 #include "kernels.h"
 #include "tc.cuh"
@@ -71,7 +73,10 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
   // 1024-align by OFFSET (not by pointer round-trip) so the compiler keeps the shared address space -> LDS
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   __shared__ uint64_t full_bar[2];
-  __shared__ float spool[2][kDwMaxGroup][kDwCB];
+  const int nwarps_ = blockDim.x >> 5;
+  // pool slots [stage][warp][image in group][channel], after the two operand stages
+  float* spool = reinterpret_cast<float*>(smem + 2 * p.stage_stride);
+  const int spool_stage = nwarps_ * p.gimg * kDwCB;
 
   constexpr int PAD = (K - 1) / 2;
   constexpr int PADE = (S == 2) ? 2 : PAD;   // stride 2: the box starts on an even column
@@ -90,7 +95,7 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
     mbar_init(&full_bar[1], 1);
     fence_barrier_init();
   }
-  for (int i = tid; i < 2 * kDwMaxGroup * kDwCB; i += blockDim.x) (&spool[0][0][0])[i] = 0.f;
+  for (int i = tid; i < 2 * spool_stage; i += blockDim.x) spool[i] = 0.f;
   __syncthreads();
 
   // tile index -> (cb fastest, then tile x, tile y, image group): neighbouring CTAs read the same pixels'
@@ -238,9 +243,12 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
         unpack2(ps, s0, s1);
         s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
         s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
-        if (xs == 0) {
-          atomicAdd(&spool[stage][g][cp * 2], s0);
-          atomicAdd(&spool[stage][g][cp * 2 + 1], s1);
+        if (xs == 0) {  // this thread is the only writer of its (warp, *, cp) slots: plain read-modify-write
+          float2* slot = reinterpret_cast<float2*>(spool + stage * spool_stage + (warp * p.gimg + g) * kDwCB + cp * 2);
+          float2 o = *slot;
+          o.x += s0;
+          o.y += s1;
+          *slot = o;
         }
       }
     }
@@ -248,11 +256,15 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
     if (p.pool != nullptr) {
       for (int i = tid; i < p.gimg * kDwCB; i += blockDim.x) {
         const int g = i >> 5, cc = i & 31;
-        const float v = spool[stage][g][cc];
-        spool[stage][g][cc] = 0.f;
+        float* sl = spool + stage * spool_stage + g * kDwCB + cc;
+        float v = 0.f;
+        for (int wq = 0; wq < nwarps_; ++wq) {  // fixed order -> deterministic
+          v += sl[wq * p.gimg * kDwCB];
+          sl[wq * p.gimg * kDwCB] = 0.f;
+        }
         const int c = cur.cb * kDwCB + cc;
         const int img = cur.ng * p.gimg + g;
-        if (c < p.C && img < p.n) atomicAdd(p.pool + (size_t)img * p.C + c, v);
+        if (c < p.C && img < p.n) pool_add(p.pool + (size_t)img * p.C + c, v);
       }
     }
     cur = nxt;
@@ -332,12 +344,12 @@ int dw_tma_occupancy_dispatch(int k, int stride, int th, int block, size_t smem)
   return 1;
 }
 
-constexpr size_t kDwBoxLimit = 54 * 1024;  // bytes per stage: 2 stages x <= 54 KB -> 2 CTAs per SM
+constexpr size_t kDwSmemLimit = 110 * 1024;  // per CTA (2 operand stages + pool slots) -> 2 CTAs per SM
 
 }  // namespace
 
 int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                    const float* bias, void* out, float* pool) {
+                    const float* bias, void* out, pool_t* pool) {
   if (n <= 0 || c % 8 || (k != 3 && k != 5) || (stride != 1 && stride != 2)) return -1;
   if (stride == 2 && (w & 1)) return -1;
   const int pad = (k - 1) / 2;
@@ -368,7 +380,7 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
       const bool whole = tiles_x == 1 && m == strips_total;  // the tile is the whole image
       for (int g = 1; g <= (whole ? kDwMaxGroup : 1); g *= 2) {
         if (g > n && g > 1) break;
-        if (bytes * g > kDwBoxLimit) break;
+        if (2 * ((bytes * g + 1023) & ~size_t(1023)) + 2 * 8 * (size_t)g * kDwCB * 4 + 1024 > kDwSmemLimit) break;
         const int items = (otw / 2) * m * g;
         double eff = (double)std::min(otw, Wo) * std::min(oth, Ho) * stride * stride / ((double)bytes / 64.0);
         double score = eff * std::min(1.0, 0.5 + items / 32.0);
@@ -412,7 +424,7 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
   plan.k = k; plan.stride = stride; plan.th = th;
   const int items = (b_otw / 2) * b_m * b_g;
   plan.block = items >= 8 ? 256 : (items >= 4 ? 128 : 64);
-  plan.smem = 1024 + 2 * (size_t)p.stage_stride;
+  plan.smem = 1024 + 2 * (size_t)p.stage_stride + 2 * (size_t)(plan.block / 32) * b_g * kDwCB * sizeof(float);
   const long long total = (long long)p.tiles_x * p.tiles_y * p.ncb * ((n + b_g - 1) / b_g);
   const int per_sm = dw_tma_occupancy_dispatch(k, stride, th, plan.block, plan.smem);
   long long grid = std::min<long long>(total, (long long)kNumSMs * per_sm);

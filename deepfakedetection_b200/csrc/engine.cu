@@ -395,6 +395,10 @@ extern "C" int b200df_finalize(b200df_handle h, int precision) {
   if (const char* env = getenv("B200DF_GEMM")) {  // debugging aid: force the SIMT GEMM on the bf16 path
     if (strcmp(env, "simt") == 0) h->gemm_impl = 1;
   }
+  h->dw_impl = 0;
+  if (const char* env = getenv("B200DF_DW")) {  // debugging aid: force the plain (non-TMA) depthwise kernel
+    if (strcmp(env, "plain") == 0) h->dw_impl = 1;
+  }
   return B200DF_OK;
 }
 
@@ -417,7 +421,7 @@ static Workspace layout_workspace(const b200df_engine* h, int n) {
   w.e = off; off += al(e * n * es);
   w.d = off; off += al(d * n * es);
   w.a = off; off += al((size_t)1280 * hw * n * es);
-  w.pool = off; off += al(h->pool_floats_per_img * n * sizeof(float));
+  w.pool = off; off += al(h->pool_floats_per_img * n * sizeof(pool_t));
   w.gate = off; off += al(h->pool_floats_per_img * n * sizeof(float));
   w.pooled = off; off += al((size_t)1280 * n * sizeof(float));
   w.logits = off; off += al((size_t)h->num_classes * n * sizeof(float));
@@ -510,9 +514,9 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
     h->plan.n = n;
     h->plan.ws = ws;
   }
-  float* pool = reinterpret_cast<float*>(ws + W.pool);
+  pool_t* pool = reinterpret_cast<pool_t*>(ws + W.pool);
   float* gate = reinterpret_cast<float*>(ws + W.gate);
-  CU_OK(cudaMemsetAsync(pool, 0, h->pool_floats_per_img * n * sizeof(float), s));
+  CU_OK(cudaMemsetAsync(pool, 0, h->pool_floats_per_img * n * sizeof(pool_t), s));
   void* cur = ws + W.t0;
   void* nxt = ws + W.t1;
   const double es = h->precision == B200DF_PREC_BF16 ? 2.0 : 4.0;
@@ -543,12 +547,12 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
       prof_end(pr, s);
       dw_in = ws + W.e;
     }
-    float* pool_b = pool + d.pool_off * n;
+    pool_t* pool_b = pool + d.pool_off * n;
     float* gate_b = gate + d.pool_off * n;
     pr = prof_begin(h, s, "dw", li, ((double)m_in + (double)m_out) * b.mid * es, 2.0 * m_out * b.mid * b.k * b.k);
     {
       bool done = false;
-      if (dt == kBF16) {
+      if (dt == kBF16 && h->dw_impl == 0) {
         if (h->plan.dws.size() != h->blocks.size()) h->plan.dws.assign(h->blocks.size(), DwPlan());
         DwPlan& dp = h->plan.dws[i];
         if (dp.x != dw_in || dp.p.n != n || dp.p.pool != pool_b) {
@@ -789,12 +793,12 @@ extern "C" int b200df_k_stem(const float* x_nchw, int n, int h, int w, const flo
 }
 
 extern "C" int b200df_k_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                               const float* bias, void* out, float* pool, int dtype, void* stream) {
+                               const float* bias, void* out, long long* pool, int dtype, void* stream) {
   CU_OK(launch_dwconv(x, n, h, w, c, k, stride, wgt, bias, out, pool, dtype, S(stream)));
   return B200DF_OK;
 }
 
-extern "C" int b200df_k_se(const float* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
+extern "C" int b200df_k_se(const long long* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
                            const float* w2t, const float* b2, float* gate, void* stream) {
   CU_OK(launch_se(pool, n, c, rd, inv_hw, w1, b1, w2t, b2, gate, S(stream)));
   return B200DF_OK;

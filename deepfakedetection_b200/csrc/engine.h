@@ -87,6 +87,7 @@ struct b200df_engine {
   float* fc_b = nullptr;
   size_t pool_floats_per_img = 0;
   int gemm_impl = 0;  // 0 = tcgen05 (bf16), 1 = SIMT
+  int dw_impl = 0;    // 0 = TMA halo kernel (bf16), 1 = plain kernel
   b200df::Plan plan;
   // profiling (off by default; never on inside a timed region)
   bool profile = false;

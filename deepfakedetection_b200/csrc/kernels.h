@@ -21,8 +21,10 @@ cudaError_t launch_stem_u8(const uint8_t* x_hwc, int n, int h, int w, const floa
                            float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, void* out,
                            int dtype, cudaStream_t s);
 
+// Pooled sums are Q24 fixed-point int64 (common.cuh: pool_t), accumulated with integer atomics.
+typedef long long pool_t;
 cudaError_t launch_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                          const float* bias, void* out, float* pool, int dtype, cudaStream_t s);
+                          const float* bias, void* out, pool_t* pool, int dtype, cudaStream_t s);
 
 struct DwTmaParams {
   int C, Ho, Wo;
@@ -39,7 +41,7 @@ struct DwTmaParams {
   const float* wgt;      // [k*k, C] fp32, BN folded
   const float* bias;     // [C]
   void* out;               // [n, Ho, Wo, C]
-  float* pool;           // [n, C] or nullptr
+  pool_t* pool;          // [n, C] Q24 sums or nullptr
 };
 
 // A planned depthwise launch: tensor map + tile geometry for one (layer, n, buffers) combination.
@@ -53,13 +55,13 @@ struct DwPlan {
 };
 // bf16 only.  Returns 0 on success (plan filled), <0 if this shape is not supported by the TMA kernel.
 int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                    const float* bias, void* out, float* pool);
+                    const float* bias, void* out, pool_t* pool);
 cudaError_t launch_dwconv_tma(const DwPlan& plan, cudaStream_t s);
 // Generic N-d bf16 tensor map (dims/strides innermost first; strides[0] is implicit).  0 on success.
 int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsigned long long* dims,
                         const unsigned long long* strides_bytes, const unsigned* box, int swizzle);
 
-cudaError_t launch_se(const float* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
+cudaError_t launch_se(const pool_t* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
                       const float* w2, const float* b2, float* gate, cudaStream_t s);
 
 cudaError_t launch_pwconv_simt(const void* x, long long m, int cin, int cout, const void* wgt, const float* bias,

@@ -11,7 +11,7 @@ namespace b200df {
 constexpr int kSeThreads = 256;
 
 __global__ void __launch_bounds__(kSeThreads)
-se_kernel(const float* __restrict__ pool, int C, int RD, float inv_hw, const float* __restrict__ w1,
+se_kernel(const pool_t* __restrict__ pool, int C, int RD, float inv_hw, const float* __restrict__ w1,
           const float* __restrict__ b1, const float* __restrict__ w2t, const float* __restrict__ b2,
           float* __restrict__ gate) {
   extern __shared__ float sm[];
@@ -19,7 +19,7 @@ se_kernel(const float* __restrict__ pool, int C, int RD, float inv_hw, const flo
   float* hid = sm + C;    // [RD]
   const int n = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int c = tid; c < C; c += kSeThreads) mean[c] = pool[(size_t)n * C + c] * inv_hw;
+  for (int c = tid; c < C; c += kSeThreads) mean[c] = pool_value(pool[(size_t)n * C + c]) * inv_hw;
   __syncthreads();
   for (int j = warp; j < RD; j += kSeThreads / 32) {
     const float* wr = w1 + (size_t)j * C;
@@ -36,7 +36,7 @@ se_kernel(const float* __restrict__ pool, int C, int RD, float inv_hw, const flo
   }
 }
 
-cudaError_t launch_se(const float* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
+cudaError_t launch_se(const pool_t* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
                       const float* w2t, const float* b2, float* gate, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   se_kernel<<<n, kSeThreads, (c + rd) * sizeof(float), s>>>(pool, c, rd, inv_hw, w1, b1, w2t, b2, gate);

@@ -224,7 +224,10 @@ class B200EfficientNetB0(nn.Module):
             images = images.float()
         self._ready(images.device)
         if torch.is_grad_enabled():
-            a = ops.trunk(images, self._engine_id)
+            # Grad-CAM hook protocol (web_ui.py:275-279): pytorch-grad-cam hooks `_conv_head` and calls
+            # `.register_hook` on its output, so A must be a graph leaf that requires grad.  The trunk has no
+            # backward (inference engine): gradients stop at A, which is all Grad-CAM needs.
+            a = ops.trunk(images.detach(), self._engine_id).requires_grad_(True)
             a = self.conv_head(a)
             return ops.head(a, self._engine_id)
         return ops.forward(images, self._engine_id)

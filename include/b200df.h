@@ -143,14 +143,16 @@ int b200df_profile_reset(b200df_handle h);
 int b200df_k_stem(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias,
                   void* out, int dtype, void* stream);
 
-/* Depthwise kxk (k=3|5, stride 1|2, pad (k-1)/2) + bias + SiLU; optional fp32 pooled sums
- * pool[n,c] += sum_hw(out) (must be zeroed by the caller).  wgt: [k*k, c] fp32 (tap-major). */
+/* Depthwise kxk (k=3|5, stride 1|2, pad (k-1)/2) + bias + SiLU; optional pooled sums
+ * pool[n,c] += sum_hw(out) (must be zeroed by the caller) as Q24 fixed-point int64 (value * 2^24),
+ * accumulated with integer atomics so the sums are order-independent and bit-reproducible.
+ * wgt: [k*k, c] fp32 (tap-major). */
 int b200df_k_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                    const float* bias, void* out, float* pool, int dtype, void* stream);
+                    const float* bias, void* out, long long* pool, int dtype, void* stream);
 
 /* Squeeze-excite MLP on pooled sums: gate[n,c] = sigmoid(W2 silu(W1 (pool*inv_hw) + b1) + b2).
  * w1: conv_reduce [rd,c]; w2t: conv_expand TRANSPOSED to [rd,c]. */
-int b200df_k_se(const float* pool, int n, int c, int rd, float inv_hw, const float* w1,
+int b200df_k_se(const long long* pool, int n, int c, int rd, float inv_hw, const float* w1,
                 const float* b1, const float* w2t, const float* b2, float* gate, void* stream);
 
 /* Pointwise (1x1) conv as GEMM: out[m, cout] = act( (x[m,:] * gate[m / rows_per_img, :]) . w^T + bias )

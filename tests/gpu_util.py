@@ -31,15 +31,16 @@ def k_dwconv(x, w_tap_major, bias, k, stride, dt, pool=True):
     pad = (k - 1) // 2
     ho, wo = (h + 2 * pad - k) // stride + 1, (wd + 2 * pad - k) // stride + 1
     out = torch.empty((n, ho, wo, c), dtype=tdtype(dt), device=x.device)
-    pl = torch.zeros((n, c), dtype=torch.float32, device=x.device) if pool else None
+    pl = torch.zeros((n, c), dtype=torch.int64, device=x.device) if pool else None  # Q24 fixed point
     _lib.check(_lib.lib().b200df_k_dwconv(P(x), n, h, wd, c, k, stride, P(w_tap_major), P(bias), P(out), P(pl), dt, stream()))
-    return out, pl
+    return out, (pl.double() / 2.0**24).float() if pool else None
 
 
 def k_se(pool, inv_hw, w1, b1, w2t, b2):
     n, c = pool.shape
     gate = torch.empty_like(pool)
-    _lib.check(_lib.lib().b200df_k_se(P(pool), n, c, w1.shape[0], C.c_float(inv_hw), P(w1), P(b1), P(w2t), P(b2), P(gate), stream()))
+    q = (pool.double() * 2.0**24).round().to(torch.int64)
+    _lib.check(_lib.lib().b200df_k_se(P(q), n, c, w1.shape[0], C.c_float(inv_hw), P(w1), P(b1), P(w2t), P(b2), P(gate), stream()))
     return gate
 
 
