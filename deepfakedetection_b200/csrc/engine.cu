@@ -249,14 +249,10 @@ int choose_bn(int cout, int* cout_pad) {
     *cout_pad = pad;
     return pad;
   }
-  for (int t = 2; t <= 64; ++t) {
-    if (pad % (16 * t) == 0 && pad / t <= 256) {
-      *cout_pad = pad;
-      return pad / t;
-    }
-  }
+  // several N tiles: the epilogue's 64-column TMA-store boxes must not reach into the next tile's
+  // columns, so the N tile is a multiple of 64 (padded weight rows are zero, padded columns are clipped)
   int t = (pad + 255) / 256;
-  int bn = ((pad + t - 1) / t + 15) / 16 * 16;
+  int bn = ((pad + t - 1) / t + 63) / 64 * 64;
   *cout_pad = bn * t;
   return bn;
 }
@@ -486,7 +482,9 @@ int run_gemm(b200df_engine* h, const GemmCall& g, int index, cudaStream_t s) {
     memset(&a, 0, sizeof(a));
     int r1 = encode_tmap_2d_bf16(a.tmap_a, g.x, g.m, g.L->cin, 128);
     int r2 = encode_tmap_2d_bf16(a.tmap_b, g.L->w, g.L->cout_pad, g.L->cin, g.L->bn);
-    if (r1 || r2) return fail(B200DF_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d) for gemm %d", r1, r2, index);
+    int r3 = encode_tmap_2d_bf16(a.tmap_out, g.out, g.m, g.L->cout, 32);
+    if (r1 || r2 || r3)
+      return fail(B200DF_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d, %d) for gemm %d", r1, r2, r3, index);
     a.m = g.m;
     a.cin = g.L->cin;
     a.cout = g.L->cout;
@@ -821,6 +819,7 @@ extern "C" int b200df_k_pwconv(const void* x, long long m, int cin, int cout, co
   CU_OK(cudaMalloc(&wpad, (size_t)cout_pad * cin * 2));
   CU_OK(cudaMalloc(&bpad, (size_t)cout_pad * sizeof(float)));
   cudaStream_t s = S(stream);
+
   CU_OK(cudaMemsetAsync(wpad, 0, (size_t)cout_pad * cin * 2, s));
   CU_OK(cudaMemsetAsync(bpad, 0, (size_t)cout_pad * sizeof(float), s));
   CU_OK(cudaMemcpyAsync(wpad, wgt, (size_t)cout * cin * 2, cudaMemcpyDeviceToDevice, s));
@@ -829,9 +828,10 @@ extern "C" int b200df_k_pwconv(const void* x, long long m, int cin, int cout, co
   memset(&a, 0, sizeof(a));
   int r1 = encode_tmap_2d_bf16(a.tmap_a, x, m, cin, 128);
   int r2 = encode_tmap_2d_bf16(a.tmap_b, wpad, cout_pad, cin, bn);
+  int r3 = encode_tmap_2d_bf16(a.tmap_out, out, m, cout, 32);
   int rc = B200DF_OK;
-  if (r1 || r2) {
-    rc = fail(B200DF_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d)", r1, r2);
+  if (r1 || r2 || r3) {
+    rc = fail(B200DF_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d, %d)", r1, r2, r3);
   } else {
     a.m = m; a.cin = cin; a.cout = cout; a.cout_pad = cout_pad; a.bn = bn;
     a.bias = bpad; a.gate = gate; a.rows_per_img = rows_per_img; a.residual = residual; a.act = act; a.out = out;

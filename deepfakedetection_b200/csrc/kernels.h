@@ -74,13 +74,14 @@ struct TcGemmArgs {
   // CUtensorMap is 128 bytes, 64-byte aligned; kept opaque here.
   alignas(64) unsigned char tmap_a[128];
   alignas(64) unsigned char tmap_b[128];
+  alignas(64) unsigned char tmap_out[128];  // [m, cout] bf16, box [32 rows, 64 cols] (epilogue TMA store)
   long long m;        // rows of A / out
   int cin;            // K
   int cout;           // valid output columns (row pitch of out / residual)
   int cout_pad;       // rows of the padded weight matrix (multiple of bn)
   int bn;             // N tile (multiple of 16, <= 256), divides cout_pad
   const float* bias;  // [cout_pad]
-  const float* gate;  // [m / rows_per_img, cin] or nullptr
+  const float* gate;  // fp32 [m / rows_per_img, cin] or nullptr
   int rows_per_img;
   const void* residual;  // bf16 [m, cout] or nullptr
   int act;               // 0 none, 1 SiLU

@@ -5,16 +5,21 @@
 // (/root/reference/orchestration/orchestrator.py:590).
 //
 // Shape of the problem: M = n*H*W rows (up to 3.2 M), K = Cin in [16, 1152], N = Cout in [16, 1280].
-// Every one of these GEMMs except conv_head is HBM-bound, so the kernel is built to stream:
+// Every one of these GEMMs except conv_head is HBM/L2-bound with a tiny K x N, so the kernel is a
+// streaming pipeline whose cost is the EPILOGUE, not the MMA:
 //   * persistent CTAs, static round-robin over (m_tile, n_tile) tiles of 128 x BN;
 //   * warp 0: TMA producer -- A tile [128 x 64] and B tile [BN x 64] per K chunk, 128B swizzle,
 //     multi-stage mbarrier ring; K / M / N tails are zero-filled by TMA out-of-bounds handling;
 //   * warp 1: one lane issues tcgen05.mma (M=128, N=BN, K=16) into a double-buffered TMEM
 //     accumulator and commits to the ring's `empty` barriers and to `tmem_full`;
-//   * warps 4-7: epilogue -- tcgen05.ld 32x32b, +bias, SiLU, +residual (fp32), bf16 pack, transpose
-//     through a warp-private swizzled smem tile so global stores are 128 B contiguous per row;
-//   * (gated variant) warps 8-11 multiply the landed A tile in place by the per-image SE gate and
-//     hand it to the MMA warp through a second barrier (fence.proxy.async before the arrive).
+//   * warps 4-7 and 8-11: TWO epilogue groups, one per TMEM accumulator, alternating tiles --
+//     tcgen05.ld 32x32b, bias from shared memory, packed f32x2 math, SiLU = h + h*tanh(h) (one MUFU),
+//     +residual, cvt.rn.bf16x2, swizzled staging tile, then ONE TMA store (cp.async.bulk.tensor
+//     shared -> global) per 32 x 64 block: no per-element address math, M / N tails clipped by the
+//     tensor map;
+//   * (gated variant) warps 12-15 multiply the landed A tile in place by the per-image fp32 SE gate
+//     (packed f32x2 multiplies, product rounded once to bf16) and hand it to the MMA warp
+//     through a second barrier (fence.proxy.async before the arrive).
 // A [m, cin] and W [cout_pad, cin] are bf16 row-major (K-major operands, no transposes anywhere).
 #include "common.cuh"
 #include "kernels.h"
@@ -30,31 +35,65 @@ constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kABytes = kBM * kBK * 2;  // 16 KB
 constexpr int kMaxStages = 8;
+constexpr int kEpiWarps = 8;              // two groups of four (one group per TMEM accumulator)
 constexpr int kEpiStageBytes = 32 * 128;  // per epilogue warp: 32 rows x 64 bf16
+constexpr int kMaxBiasFloats = 1536;
 
 struct TcParams {
   int m, cin, cout, cout_pad, bn;
   int m_tiles, n_tiles, k_chunks, stages;
   uint32_t tmem_cols;
   const float* bias;
-  const float* gate;
+  const float* gate;  // [m / rows_per_img, cin] fp32 or nullptr
   int rows_per_img;
   const bf16* residual;
   int act;
-  bf16* out;
 };
 
+typedef unsigned long long f32x2_t;
+__device__ __forceinline__ f32x2_t f2_pack(float lo, float hi) {
+  f32x2_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(f32x2_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2_t f2_add(f32x2_t a, f32x2_t b) {
+  f32x2_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2_t f2_mul(f32x2_t a, f32x2_t b) {
+  f32x2_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2_t f2_fma(f32x2_t a, f32x2_t b, f32x2_t c) {
+  f32x2_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+// two bf16 (one word) times two fp32 gates, product rounded once to bf16
+__device__ __forceinline__ uint32_t scale_bf16x2(uint32_t a, float g0, float g1) {
+  const f32x2_t pr = f2_mul(f2_pack(__uint_as_float(a << 16), __uint_as_float(a & 0xffff0000u)), f2_pack(g0, g1));
+  float lo, hi;
+  f2_unpack(pr, lo, hi);
+  return pack_bf16x2(lo, hi);
+}
+
 template <bool kGate>
-__global__ void __launch_bounds__(kGate ? 384 : 256, 1)
+__global__ void __launch_bounds__(kGate ? 512 : 384, 1)
 pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                 const TcParams p) {
+                 const __grid_constant__ CUtensorMap tmap_out, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-B align the operand ring (128B swizzle atoms are 1024 B)
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int b_bytes = p.bn * kBK * 2;
   const int stage_bytes = kABytes + b_bytes;
-  uint8_t* epi_smem = smem + (size_t)p.stages * stage_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + 4 * kEpiStageBytes);
+  uint8_t* epi_smem = smem + (size_t)p.stages * stage_bytes;  // 1024-aligned: stage_bytes % 1024 == 0
+  float* sbias = reinterpret_cast<float*>(epi_smem + kEpiWarps * kEpiStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sbias + kMaxBiasFloats);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kMaxStages;
   uint64_t* scaled_bar = bars + 2 * kMaxStages;
@@ -68,6 +107,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    tma_prefetch_desc(&tmap_out);
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -83,6 +123,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     tmem_alloc(tmem_ptr, p.tmem_cols);
     tmem_relinquish();
   }
+  for (int i = threadIdx.x; i < p.cout_pad; i += blockDim.x) sbias[i] = __ldg(p.bias + i);
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -137,22 +178,25 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (++s == p.stages) { s = 0; ph ^= 1; }
       }
     }
-  } else if (warp >= 4 && warp < 8) {
-    // ================= epilogue =================
+  } else if (warp >= 4 && warp < 4 + kEpiWarps) {
+    // ================= epilogue (group = accumulator) =================
+    const int grp = (warp - 4) >> 2;
     const int q = warp & 3;  // TMEM lane quarter this warp may touch
-    uint8_t* stg = epi_smem + q * kEpiStageBytes;
+    uint8_t* stg = epi_smem + (warp - 4) * kEpiStageBytes;
     const uint32_t stg_u32 = smem_u32(stg);
+    const f32x2_t half2 = f2_pack(0.5f, 0.5f);
+    bool store_pending = false;
     int lt = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
+      if ((lt & 1) != grp) continue;
       const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
-      const int acc = lt & 1;
       const uint32_t acc_ph = (lt >> 1) & 1;
-      mbar_wait(&tmem_full[acc], acc_ph);
+      mbar_wait(&tmem_full[grp], acc_ph);
       tcgen05_fence_after();
       const int row0 = mt * kBM + q * 32;  // first row of this warp
       const int row = row0 + lane;
       const int ncol0 = nt * p.bn;
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * p.bn);
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * p.bn);
       for (int cb = 0; cb < p.bn; cb += 64) {
         const int ncols = min(64, p.bn - cb);  // multiple of 16
         uint32_t r[4][16];
@@ -160,91 +204,129 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         for (int g = 0; g < 4; ++g)
           if (g * 16 < ncols) tmem_ld16(t_row + (uint32_t)(cb + g * 16), r[g]);
         tmem_ld_wait();
+        if (cb + 64 >= p.bn) {  // accumulator fully read: hand it back to the MMA warp early
+          tcgen05_fence_before();
+          mbar_arrive(&tmem_empty[grp]);
+        }
+        if (store_pending) {  // the previous TMA store must have finished reading the staging tile
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          __syncwarp();
+          store_pending = false;
+        }
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           if (g * 16 < ncols) {
             const int col = ncol0 + cb + g * 16;  // global output column of r[g][0]
-            float v[16];
+            f32x2_t v[8];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[g][j]) + __ldg(p.bias + col + j);
+            for (int j4 = 0; j4 < 4; ++j4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(sbias + col + 4 * j4);  // smem broadcast
+              v[2 * j4] = f2_add(f2_pack(__uint_as_float(r[g][4 * j4]), __uint_as_float(r[g][4 * j4 + 1])),
+                                 f2_pack(b4.x, b4.y));
+              v[2 * j4 + 1] = f2_add(f2_pack(__uint_as_float(r[g][4 * j4 + 2]), __uint_as_float(r[g][4 * j4 + 3])),
+                                     f2_pack(b4.z, b4.w));
+            }
             if (p.act == 1) {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) v[j] = silu_fast(v[j]);
+              for (int j = 0; j < 8; ++j) {
+                const f32x2_t h = f2_mul(v[j], half2);
+                float h0, h1;
+                f2_unpack(h, h0, h1);
+                v[j] = f2_fma(h, f2_pack(tanh_fast(h0), tanh_fast(h1)), h);
+              }
             }
             if (p.residual != nullptr && row < p.m) {
 #pragma unroll
               for (int h = 0; h < 2; ++h) {
                 if (col + 8 * h < p.cout) {
-                  float rr[8];
-                  load8<bf16>(p.residual + (size_t)row * p.cout + col + 8 * h, rr);
+                  const uint4 rr = __ldg(reinterpret_cast<const uint4*>(p.residual + (size_t)row * p.cout + col + 8 * h));
+                  const uint32_t rw[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
-                  for (int j = 0; j < 8; ++j) v[8 * h + j] += rr[j];
+                  for (int j = 0; j < 4; ++j)
+                    v[4 * h + j] = f2_add(v[4 * h + j], f2_pack(__uint_as_float(rw[j] << 16),
+                                                                __uint_as_float(rw[j] & 0xffff0000u)));
                 }
               }
             }
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
               uint4 pk;
-              pk.x = pack_bf16x2(v[8 * h + 0], v[8 * h + 1]);
-              pk.y = pack_bf16x2(v[8 * h + 2], v[8 * h + 3]);
-              pk.z = pack_bf16x2(v[8 * h + 4], v[8 * h + 5]);
-              pk.w = pack_bf16x2(v[8 * h + 6], v[8 * h + 7]);
+              float a0, a1;
+              f2_unpack(v[4 * h + 0], a0, a1); pk.x = pack_bf16x2(a0, a1);
+              f2_unpack(v[4 * h + 1], a0, a1); pk.y = pack_bf16x2(a0, a1);
+              f2_unpack(v[4 * h + 2], a0, a1); pk.z = pack_bf16x2(a0, a1);
+              f2_unpack(v[4 * h + 3], a0, a1); pk.w = pack_bf16x2(a0, a1);
               const int chunk = g * 2 + h;
               *reinterpret_cast<uint4*>(stg + lane * 128 + ((chunk ^ (lane & 7)) << 4)) = pk;
             }
           }
         }
+        // staging tile -> global: one TMA store of the [32 rows x 64 cols] box (rows >= m and columns >= cout
+        // are clipped by the tensor map; columns past `ncols` only exist when they are >= cout, see choose_bn)
+        fence_proxy_async_smem();
         __syncwarp();
-        // coalesced copy-out: 8 lanes cover one 128-B row segment, 4 rows per instruction
-        const int j = lane & 7;
-        const int gcol = ncol0 + cb + j * 8;
-        const bool col_ok = (j * 8 < ncols) && (gcol < p.cout);
-#pragma unroll
-        for (int ps = 0; ps < 8; ++ps) {
-          const int rr = ps * 4 + (lane >> 3);
-          const int grow = row0 + rr;
-          if (col_ok && grow < p.m) {
-            uint4 pk;
-            const uint32_t a = stg_u32 + rr * 128 + ((j ^ (rr & 7)) << 4);
-            asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(pk.x), "=r"(pk.y), "=r"(pk.z), "=r"(pk.w)
-                         : "r"(a));
-            *reinterpret_cast<uint4*>(p.out + (size_t)grow * p.cout + gcol) = pk;
-          }
+        if (lane == 0) {
+          asm volatile(
+              "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                  reinterpret_cast<uint64_t>(&tmap_out)),
+              "r"(stg_u32), "r"(ncol0 + cb), "r"(row0)
+              : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
-        __syncwarp();
+        store_pending = true;
       }
-      tcgen05_fence_before();
-      mbar_arrive(&tmem_empty[acc]);
     }
-  } else if (kGate && warp >= 8) {
+    if (store_pending && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  } else if (kGate && warp >= 4 + kEpiWarps) {
     // ================= SE-gate scaler: A[m,k] *= gate[img(m), k] in shared memory =================
-    const int tr = threadIdx.x - 256;  // row of the A tile owned by this thread
+    // A thread owns ONE 16-byte K chunk (8 channels) of 8 rows (row group rg, rg+16, ...): its 8 fp32 gate
+    // values stay in registers while the rows belong to the same image, and are fetched BEFORE the wait on
+    // the TMA barrier, so the per-chunk critical path is LDS -> 4 packed multiplies -> STS.
+    const int ts = threadIdx.x - 32 * (4 + kEpiWarps);
+    const int lc = ts & 7;          // logical 16-B chunk inside the 128-B swizzled row
+    const int rg = ts >> 3;         // first row; rows rg + 16 j
+    const int pc = lc ^ (rg & 7);   // physical chunk ((rg + 16 j) & 7 == rg & 7)
     int s = 0;
     uint32_t ph = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const int mt = t / p.n_tiles;
-      const int row = mt * kBM + tr;
-      const bool row_ok = row < p.m;
-      const float* grow = p.gate + (size_t)(row_ok ? row / p.rows_per_img : 0) * p.cin;
+      const int row0 = mt * kBM + rg;
+      const int img0 = row0 / p.rows_per_img;
+      const int rem0 = row0 - img0 * p.rows_per_img;
       for (int kc = 0; kc < p.k_chunks; ++kc) {
+        const int kq = kc * (kBK / 8) + lc;  // this thread's 16-B chunk index along K
+        const bool k_ok = kq < (p.cin >> 3);
+        int img = img0, rem = rem0, img_loaded = -1;
+        float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
+        if (k_ok && row0 < p.m) {
+          const float4* gp = reinterpret_cast<const float4*>(p.gate + (size_t)img * p.cin) + 2 * kq;
+          g0 = __ldg(gp);
+          g1 = __ldg(gp + 1);
+          img_loaded = img;
+        }
         mbar_wait(&full_bar[s], ph);
-        if (row_ok) {
-          uint8_t* arow = smem + (size_t)s * stage_bytes + tr * 128;
+        if (k_ok) {
+          uint8_t* base = smem + (size_t)s * stage_bytes + rg * 128 + (pc << 4);
+          uint4 a[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int pc = (i + tr) & 7;       // physical 16-B chunk (staggered: no bank conflicts)
-            const int lc = pc ^ (tr & 7);      // logical chunk under the 128B swizzle
-            const int k0 = kc * kBK + lc * 8;
-            if (k0 < p.cin) {
-              uint4* ptr = reinterpret_cast<uint4*>(arow + (pc << 4));
-              float a[8], g[8];
-              unpack_bf16x8(*ptr, a);
-              load8<float>(grow + k0, g);
+          for (int j = 0; j < 8; ++j) a[j] = *reinterpret_cast<const uint4*>(base + j * 16 * 128);
 #pragma unroll
-              for (int e = 0; e < 8; ++e) a[e] *= g[e];
-              *ptr = pack_bf16x8(a);
+          for (int j = 0; j < 8; ++j) {
+            if (row0 + 16 * j < p.m) {
+              if (img != img_loaded) {
+                const float4* gp = reinterpret_cast<const float4*>(p.gate + (size_t)img * p.cin) + 2 * kq;
+                g0 = __ldg(gp);
+                g1 = __ldg(gp + 1);
+                img_loaded = img;
+              }
+              a[j].x = scale_bf16x2(a[j].x, g0.x, g0.y);
+              a[j].y = scale_bf16x2(a[j].y, g0.z, g0.w);
+              a[j].z = scale_bf16x2(a[j].z, g1.x, g1.y);
+              a[j].w = scale_bf16x2(a[j].w, g1.z, g1.w);
+              *reinterpret_cast<uint4*>(base + j * 16 * 128) = a[j];
             }
+            rem += 16;
+            while (rem >= p.rows_per_img) { rem -= p.rows_per_img; ++img; }
           }
         }
         fence_proxy_async_smem();
@@ -296,14 +378,14 @@ int encode_tmap_2d_bf16(void* tmap_out, const void* base, long long rows, int co
 }
 
 static size_t tc_smem_bytes(int bn, int stages) {
-  return 1024 /*align slack*/ + (size_t)stages * (kABytes + bn * kBK * 2) + 4 * kEpiStageBytes +
-         (3 * kMaxStages + 4) * sizeof(uint64_t) + 16;
+  return 1024 /*align slack*/ + (size_t)stages * (kABytes + bn * kBK * 2) + kEpiWarps * kEpiStageBytes +
+         kMaxBiasFloats * sizeof(float) + (3 * kMaxStages + 4) * sizeof(uint64_t) + 16;
 }
 
 cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   if (a.m <= 0) return cudaSuccess;
   if (a.m >= (1ll << 31) - kBM || a.bn % 16 || a.bn < 16 || a.bn > 256 || a.cout_pad % a.bn || a.cin % 8 ||
-      a.cout % 8)
+      a.cout % 8 || a.cout_pad > kMaxBiasFloats || (a.cout_pad != a.bn && a.bn % 64))
     return cudaErrorInvalidValue;
   TcParams p;
   p.m = (int)a.m;
@@ -317,7 +399,7 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * a.bn)) cols <<= 1;
   p.tmem_cols = cols;
-  const size_t budget = 200 * 1024;
+  const size_t budget = 220 * 1024;
   int stages = kMaxStages;
   while (stages > 2 && tc_smem_bytes(a.bn, stages) > budget) --stages;
   p.stages = stages;
@@ -326,12 +408,12 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   p.rows_per_img = a.rows_per_img > 0 ? a.rows_per_img : 1;
   p.residual = reinterpret_cast<const bf16*>(a.residual);
   p.act = a.act;
-  p.out = reinterpret_cast<bf16*>(a.out);
   const size_t smem = tc_smem_bytes(a.bn, stages);
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
   const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
   const CUtensorMap* ta = reinterpret_cast<const CUtensorMap*>(a.tmap_a);
   const CUtensorMap* tb = reinterpret_cast<const CUtensorMap*>(a.tmap_b);
+  const CUtensorMap* to = reinterpret_cast<const CUtensorMap*>(a.tmap_out);
   cudaError_t e;
   if (a.gate) {
     static bool attr_done = false;
@@ -340,7 +422,7 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
       if (e != cudaSuccess) return e;
       attr_done = true;
     }
-    pwconv_tc_kernel<true><<<grid, 384, smem, s>>>(*ta, *tb, p);
+    pwconv_tc_kernel<true><<<grid, 512, smem, s>>>(*ta, *tb, *to, p);
   } else {
     static bool attr_done = false;
     if (!attr_done) {
@@ -348,7 +430,7 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
       if (e != cudaSuccess) return e;
       attr_done = true;
     }
-    pwconv_tc_kernel<false><<<grid, 256, smem, s>>>(*ta, *tb, p);
+    pwconv_tc_kernel<false><<<grid, 384, smem, s>>>(*ta, *tb, *to, p);
   }
   count_launch();
   return cudaGetLastError();
