@@ -480,9 +480,10 @@ int run_gemm(b200df_engine* h, const GemmCall& g, int index, cudaStream_t s) {
   TcGemmArgs& a = h->plan.gemms[index];
   if (a.out != g.out || a.m != g.m) {  // (re)encode tensor maps for this (n, workspace)
     memset(&a, 0, sizeof(a));
-    int r1 = encode_tmap_2d_bf16(a.tmap_a, g.x, g.m, g.L->cin, 128);
+    const int rpi = g.gate ? g.rows_per_img : 0;
+    int r1 = encode_tmap_act_bf16(a.tmap_a, g.x, g.m, g.L->cin, rpi, 128);
     int r2 = encode_tmap_2d_bf16(a.tmap_b, g.L->w, g.L->cout_pad, g.L->cin, g.L->bn);
-    int r3 = encode_tmap_2d_bf16(a.tmap_out, g.out, g.m, g.L->cout, 32);
+    int r3 = encode_tmap_act_bf16(a.tmap_out, g.out, g.m, g.L->cout, rpi, 32);
     if (r1 || r2 || r3)
       return fail(B200DF_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d, %d) for gemm %d", r1, r2, r3, index);
     a.m = g.m;
@@ -826,9 +827,14 @@ extern "C" int b200df_k_pwconv(const void* x, long long m, int cin, int cout, co
   CU_OK(cudaMemcpyAsync(bpad, bias, (size_t)cout * sizeof(float), cudaMemcpyDeviceToDevice, s));
   TcGemmArgs a;
   memset(&a, 0, sizeof(a));
-  int r1 = encode_tmap_2d_bf16(a.tmap_a, x, m, cin, 128);
+  if (gate && (rows_per_img <= 0 || m % rows_per_img)) {
+    cudaFree(wpad);
+    cudaFree(bpad);
+    return fail(B200DF_E_INVALID, "gated tcgen05 GEMM needs m to be a multiple of rows_per_img");
+  }
+  int r1 = encode_tmap_act_bf16(a.tmap_a, x, m, cin, gate ? rows_per_img : 0, 128);
   int r2 = encode_tmap_2d_bf16(a.tmap_b, wpad, cout_pad, cin, bn);
-  int r3 = encode_tmap_2d_bf16(a.tmap_out, out, m, cout, 32);
+  int r3 = encode_tmap_act_bf16(a.tmap_out, out, m, cout, gate ? rows_per_img : 0, 32);
   int rc = B200DF_OK;
   if (r1 || r2 || r3) {
     rc = fail(B200DF_E_CUDA, "cuTensorMapEncodeTiled failed (%d, %d, %d)", r1, r2, r3);

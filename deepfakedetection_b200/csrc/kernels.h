@@ -74,7 +74,7 @@ struct TcGemmArgs {
   // CUtensorMap is 128 bytes, 64-byte aligned; kept opaque here.
   alignas(64) unsigned char tmap_a[128];
   alignas(64) unsigned char tmap_b[128];
-  alignas(64) unsigned char tmap_out[128];  // [m, cout] bf16, box [32 rows, 64 cols] (epilogue TMA store)
+  alignas(64) unsigned char tmap_out[128];  // out as [cout, rows_per_img, images], box [64, 32, 1] (TMA store)
   long long m;        // rows of A / out
   int cin;            // K
   int cout;           // valid output columns (row pitch of out / residual)
@@ -87,8 +87,12 @@ struct TcGemmArgs {
   int act;               // 0 none, 1 SiLU
   void* out;             // bf16 [m, cout]
 };
-// Encodes a 2D bf16 row-major [rows, cols] tensor map with box [box_rows, 64] and 128B swizzle.
+// Encodes a 2D bf16 row-major [rows, cols] tensor map with box [box_rows, 64] and 128B swizzle (weights).
 int encode_tmap_2d_bf16(void* tmap_out, const void* base, long long rows, int cols, int box_rows);
+// Activation / output operand [m, cols] viewed as [images, rows_per_img, cols] (3-D map, box [1, box_rows, 64],
+// 128B swizzle) so that M tiles never straddle two images: rows past an image's end are zero-filled on load
+// and clipped on store.  rows_per_img <= 0 (ungated GEMM) means one "image" of m rows.  m % rows_per_img == 0.
+int encode_tmap_act_bf16(void* tmap_out, const void* base, long long m, int cols, int rows_per_img, int box_rows);
 cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s);
 
 cudaError_t launch_head_pool(const void* a, int n, int hw, int c, const float* scale, const float* shift,

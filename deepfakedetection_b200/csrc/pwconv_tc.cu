@@ -36,16 +36,18 @@ constexpr int kBK = 64;
 constexpr int kABytes = kBM * kBK * 2;  // 16 KB
 constexpr int kMaxStages = 8;
 constexpr int kEpiWarps = 8;              // two groups of four (one group per TMEM accumulator)
-constexpr int kEpiStageBytes = 32 * 128;  // per epilogue warp: 32 rows x 64 bf16
+constexpr int kEpiStageBytes = 32 * 128;  // one staging tile: 32 rows x 64 bf16; TWO per epilogue warp
 constexpr int kMaxBiasFloats = 1536;
 
 struct TcParams {
   int m, cin, cout, cout_pad, bn;
+  int rpi;            // rows per image (ungated: m, one "image")
+  int tiles_per_img;  // ceil(rpi / 128): M tiles never straddle images
+  int scale_b;        // gated only: 1 = fold the gate into the B (weight) tile, 0 = into the A tile
   int m_tiles, n_tiles, k_chunks, stages;
   uint32_t tmem_cols;
   const float* bias;
   const float* gate;  // [m / rows_per_img, cin] fp32 or nullptr
-  int rows_per_img;
   const bf16* residual;
   int act;
 };
@@ -92,7 +94,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int b_bytes = p.bn * kBK * 2;
   const int stage_bytes = kABytes + b_bytes;
   uint8_t* epi_smem = smem + (size_t)p.stages * stage_bytes;  // 1024-aligned: stage_bytes % 1024 == 0
-  float* sbias = reinterpret_cast<float*>(epi_smem + kEpiWarps * kEpiStageBytes);
+  float* sbias = reinterpret_cast<float*>(epi_smem + 2 * kEpiWarps * kEpiStageBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(sbias + kMaxBiasFloats);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kMaxStages;
@@ -136,11 +138,12 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       uint32_t ph = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
+        const int img = mt / p.tiles_per_img, lrow0 = (mt - img * p.tiles_per_img) * kBM;
         for (int kc = 0; kc < p.k_chunks; ++kc) {
           mbar_wait(&empty_bar[s], ph ^ 1);
           uint8_t* sa = smem + (size_t)s * stage_bytes;
           mbar_arrive_expect_tx(&full_bar[s], (uint32_t)stage_bytes);
-          tma_load_2d(sa, &tmap_a, kc * kBK, mt * kBM, &full_bar[s]);
+          tma_load_3d(sa, &tmap_a, kc * kBK, lrow0, img, &full_bar[s]);
           tma_load_2d(sa + kABytes, &tmap_b, kc * kBK, nt * p.bn, &full_bar[s]);
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
@@ -182,10 +185,9 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // ================= epilogue (group = accumulator) =================
     const int grp = (warp - 4) >> 2;
     const int q = warp & 3;  // TMEM lane quarter this warp may touch
-    uint8_t* stg = epi_smem + (warp - 4) * kEpiStageBytes;
-    const uint32_t stg_u32 = smem_u32(stg);
+    uint8_t* stg_base = epi_smem + (warp - 4) * 2 * kEpiStageBytes;
     const f32x2_t half2 = f2_pack(0.5f, 0.5f);
-    bool store_pending = false;
+    int stores = 0;  // TMA stores issued by this warp (staging buffer = stores & 1)
     int lt = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++lt) {
       if ((lt & 1) != grp) continue;
@@ -193,8 +195,10 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const uint32_t acc_ph = (lt >> 1) & 1;
       mbar_wait(&tmem_full[grp], acc_ph);
       tcgen05_fence_after();
-      const int row0 = mt * kBM + q * 32;  // first row of this warp
-      const int row = row0 + lane;
+      const int img = mt / p.tiles_per_img;
+      const int lrow0 = (mt - img * p.tiles_per_img) * kBM + q * 32;  // first row of this warp inside the image
+      const bool row_ok = lrow0 + lane < p.rpi;
+      const size_t row = (size_t)img * p.rpi + lrow0 + lane;         // global row of this lane
       const int ncol0 = nt * p.bn;
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * p.bn);
       for (int cb = 0; cb < p.bn; cb += 64) {
@@ -208,10 +212,10 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           tcgen05_fence_before();
           mbar_arrive(&tmem_empty[grp]);
         }
-        if (store_pending) {  // the previous TMA store must have finished reading the staging tile
-          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        uint8_t* stg = stg_base + (stores & 1) * kEpiStageBytes;
+        if (stores >= 2) {  // the store issued two blocks ago must have finished READING this staging tile
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
           __syncwarp();
-          store_pending = false;
         }
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
@@ -235,11 +239,11 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 v[j] = f2_fma(h, f2_pack(tanh_fast(h0), tanh_fast(h1)), h);
               }
             }
-            if (p.residual != nullptr && row < p.m) {
+            if (p.residual != nullptr && row_ok) {
 #pragma unroll
               for (int h = 0; h < 2; ++h) {
                 if (col + 8 * h < p.cout) {
-                  const uint4 rr = __ldg(reinterpret_cast<const uint4*>(p.residual + (size_t)row * p.cout + col + 8 * h));
+                  const uint4 rr = __ldg(reinterpret_cast<const uint4*>(p.residual + row * p.cout + col + 8 * h));
                   const uint32_t rw[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
                   for (int j = 0; j < 4; ++j)
@@ -267,21 +271,24 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         __syncwarp();
         if (lane == 0) {
           asm volatile(
-              "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+              "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
                   reinterpret_cast<uint64_t>(&tmap_out)),
-              "r"(stg_u32), "r"(ncol0 + cb), "r"(row0)
+              "r"(smem_u32(stg)), "r"(ncol0 + cb), "r"(lrow0), "r"(img)
               : "memory");
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
-        store_pending = true;
+        ++stores;
       }
     }
-    if (store_pending && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (stores > 0 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   } else if (kGate && warp >= 4 + kEpiWarps) {
-    // ================= SE-gate scaler: A[m,k] *= gate[img(m), k] in shared memory =================
-    // A thread owns ONE 16-byte K chunk (8 channels) of 8 rows (row group rg, rg+16, ...): its 8 fp32 gate
-    // values stay in registers while the rows belong to the same image, and are fetched BEFORE the wait on
-    // the TMA barrier, so the per-chunk critical path is LDS -> 4 packed multiplies -> STS.
+    // ================= SE-gate scaler =================
+    // M tiles never straddle images, so ONE gate vector applies to a whole tile and the gate can be folded
+    // into whichever operand tile is smaller:  sum_k (a_k g_k) w_k  ==  sum_k a_k (g_k w_k).
+    //   scale_b: B tile [BN x 64] (weights) *= gate   -- the big-spatial layers, BN = 16..96 rows
+    //   else   : A tile [rows x 64] (activations) *= gate -- only the image's valid rows
+    // A thread owns ONE 16-byte K chunk (8 channels): its 8 fp32 gate values are fetched BEFORE the wait on
+    // the TMA barrier and stay in registers for all of its rows (rows ts/8, ts/8 + 16, ...).
     const int ts = threadIdx.x - 32 * (4 + kEpiWarps);
     const int lc = ts & 7;          // logical 16-B chunk inside the 128-B swizzled row
     const int rg = ts >> 3;         // first row; rows rg + 16 j
@@ -290,43 +297,36 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint32_t ph = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const int mt = t / p.n_tiles;
-      const int row0 = mt * kBM + rg;
-      const int img0 = row0 / p.rows_per_img;
-      const int rem0 = row0 - img0 * p.rows_per_img;
+      const int img = mt / p.tiles_per_img;
+      const int lrow0 = (mt - img * p.tiles_per_img) * kBM;
+      const int nrows = p.scale_b ? p.bn : min(kBM, p.rpi - lrow0);  // rows of the tile to scale
+      const float4* gimg = reinterpret_cast<const float4*>(p.gate + (size_t)img * p.cin);
       for (int kc = 0; kc < p.k_chunks; ++kc) {
         const int kq = kc * (kBK / 8) + lc;  // this thread's 16-B chunk index along K
         const bool k_ok = kq < (p.cin >> 3);
-        int img = img0, rem = rem0, img_loaded = -1;
         float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;
-        if (k_ok && row0 < p.m) {
-          const float4* gp = reinterpret_cast<const float4*>(p.gate + (size_t)img * p.cin) + 2 * kq;
-          g0 = __ldg(gp);
-          g1 = __ldg(gp + 1);
-          img_loaded = img;
+        if (k_ok) {
+          g0 = __ldg(gimg + 2 * kq);
+          g1 = __ldg(gimg + 2 * kq + 1);
         }
         mbar_wait(&full_bar[s], ph);
         if (k_ok) {
-          uint8_t* base = smem + (size_t)s * stage_bytes + rg * 128 + (pc << 4);
-          uint4 a[8];
+          uint8_t* base = smem + (size_t)s * stage_bytes + (p.scale_b ? kABytes : 0) + rg * 128 + (pc << 4);
+          for (int r0 = rg; r0 < nrows; r0 += 64, base += 64 * 128) {
+            uint4 a[4];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) a[j] = *reinterpret_cast<const uint4*>(base + j * 16 * 128);
+            for (int j = 0; j < 4; ++j)
+              if (r0 + 16 * j < nrows) a[j] = *reinterpret_cast<const uint4*>(base + j * 16 * 128);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            if (row0 + 16 * j < p.m) {
-              if (img != img_loaded) {
-                const float4* gp = reinterpret_cast<const float4*>(p.gate + (size_t)img * p.cin) + 2 * kq;
-                g0 = __ldg(gp);
-                g1 = __ldg(gp + 1);
-                img_loaded = img;
+            for (int j = 0; j < 4; ++j) {
+              if (r0 + 16 * j < nrows) {
+                a[j].x = scale_bf16x2(a[j].x, g0.x, g0.y);
+                a[j].y = scale_bf16x2(a[j].y, g0.z, g0.w);
+                a[j].z = scale_bf16x2(a[j].z, g1.x, g1.y);
+                a[j].w = scale_bf16x2(a[j].w, g1.z, g1.w);
+                *reinterpret_cast<uint4*>(base + j * 16 * 128) = a[j];
               }
-              a[j].x = scale_bf16x2(a[j].x, g0.x, g0.y);
-              a[j].y = scale_bf16x2(a[j].y, g0.z, g0.w);
-              a[j].z = scale_bf16x2(a[j].z, g1.x, g1.y);
-              a[j].w = scale_bf16x2(a[j].w, g1.z, g1.w);
-              *reinterpret_cast<uint4*>(base + j * 16 * 128) = a[j];
             }
-            rem += 16;
-            while (rem >= p.rows_per_img) { rem -= p.rows_per_img; ++img; }
           }
         }
         fence_proxy_async_smem();
@@ -377,8 +377,17 @@ int encode_tmap_2d_bf16(void* tmap_out, const void* base, long long rows, int co
   return r == CUDA_SUCCESS ? 0 : -3;
 }
 
+int encode_tmap_act_bf16(void* tmap_out, const void* base, long long m, int cols, int rows_per_img, int box_rows) {
+  const long long rpi = rows_per_img > 0 ? rows_per_img : m;
+  if (m <= 0 || m % rpi || (cols % 8) || box_rows > 256) return -2;
+  unsigned long long dims[3] = {(unsigned long long)cols, (unsigned long long)rpi, (unsigned long long)(m / rpi)};
+  unsigned long long str[3] = {2, (unsigned long long)cols * 2, (unsigned long long)rpi * cols * 2};
+  unsigned box[3] = {(unsigned)kBK, (unsigned)box_rows, 1};
+  return encode_tmap_nd_bf16(tmap_out, base, 3, dims, str, box, 128);
+}
+
 static size_t tc_smem_bytes(int bn, int stages) {
-  return 1024 /*align slack*/ + (size_t)stages * (kABytes + bn * kBK * 2) + kEpiWarps * kEpiStageBytes +
+  return 1024 /*align slack*/ + (size_t)stages * (kABytes + bn * kBK * 2) + 2 * kEpiWarps * kEpiStageBytes +
          kMaxBiasFloats * sizeof(float) + (3 * kMaxStages + 4) * sizeof(uint64_t) + 16;
 }
 
@@ -393,7 +402,14 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   p.cout = a.cout;
   p.cout_pad = a.cout_pad;
   p.bn = a.bn;
-  p.m_tiles = (int)((a.m + kBM - 1) / kBM);
+  // M tiles are image-aligned (ungated: one image of m rows)
+  const long long rpi = (a.gate && a.rows_per_img > 0) ? a.rows_per_img : a.m;
+  if (a.m % rpi) return cudaErrorInvalidValue;
+  p.rpi = (int)rpi;
+  p.tiles_per_img = (int)((rpi + kBM - 1) / kBM);
+  p.m_tiles = (int)(a.m / rpi) * p.tiles_per_img;
+  // fold the gate into the smaller operand tile: B has bn rows, A has min(128, rpi) valid rows
+  p.scale_b = (a.gate && a.bn <= 96 && a.bn < (rpi < kBM ? rpi : kBM)) ? 1 : 0;
   p.n_tiles = a.cout_pad / a.bn;
   p.k_chunks = (a.cin + kBK - 1) / kBK;
   uint32_t cols = 32;
@@ -405,7 +421,6 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   p.stages = stages;
   p.bias = a.bias;
   p.gate = a.gate;
-  p.rows_per_img = a.rows_per_img > 0 ? a.rows_per_img : 1;
   p.residual = reinterpret_cast<const bf16*>(a.residual);
   p.act = a.act;
   const size_t smem = tc_smem_bytes(a.bn, stages);
