@@ -43,13 +43,13 @@ struct TcParams {
   int m, cin, cout, cout_pad, bn;
   int rpi;            // rows per image (ungated: m, one "image")
   int tiles_per_img;  // ceil(rpi / 128): M tiles never straddle images
+  int acc_stride;     // TMEM columns between the two accumulators (bn rounded up to 32)
   int scale_b;        // gated only: 1 = fold the gate into the B (weight) tile, 0 = into the A tile
   int m_tiles, n_tiles, k_chunks, stages;
   uint32_t tmem_cols;
   const float* bias;
   const float* gate;  // [m / rows_per_img, cin] fp32 or nullptr
   const bf16* residual;
-  int act;
 };
 
 typedef unsigned long long f32x2_t;
@@ -84,7 +84,7 @@ __device__ __forceinline__ uint32_t scale_bf16x2(uint32_t a, float g0, float g1)
   return pack_bf16x2(lo, hi);
 }
 
-template <bool kGate>
+template <bool kGate, int kAct, bool kRes>
 __global__ void __launch_bounds__(kGate ? 512 : 384, 1)
 pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_out, const TcParams p) {
@@ -160,7 +160,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const uint32_t acc_ph = (lt >> 1) & 1;
       mbar_wait(&tmem_empty[acc], acc_ph ^ 1);
       tcgen05_fence_after();
-      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.bn);
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride);
       for (int kc = 0; kc < p.k_chunks; ++kc) {
         mbar_wait(kGate ? &scaled_bar[s] : &full_bar[s], ph);
         tcgen05_fence_after();
@@ -200,73 +200,82 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const bool row_ok = lrow0 + lane < p.rpi;
       const size_t row = (size_t)img * p.rpi + lrow0 + lane;         // global row of this lane
       const int ncol0 = nt * p.bn;
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * p.bn);
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * p.acc_stride);
       for (int cb = 0; cb < p.bn; cb += 64) {
         const int ncols = min(64, p.bn - cb);  // multiple of 16
-        uint32_t r[4][16];
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-          if (g * 16 < ncols) tmem_ld16(t_row + (uint32_t)(cb + g * 16), r[g]);
-        tmem_ld_wait();
-        if (cb + 64 >= p.bn) {  // accumulator fully read: hand it back to the MMA warp early
-          tcgen05_fence_before();
-          mbar_arrive(&tmem_empty[grp]);
-        }
         uint8_t* stg = stg_base + (stores & 1) * kEpiStageBytes;
         if (stores >= 2) {  // the store issued two blocks ago must have finished READING this staging tile
           if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
           __syncwarp();
         }
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          if (g * 16 < ncols) {
-            const int col = ncol0 + cb + g * 16;  // global output column of r[g][0]
-            f32x2_t v[8];
+        for (int hb = 0; hb < 2; ++hb) {  // two 32-column halves of the 64-column staging tile
+          if (hb * 32 < ncols) {
+            const int col = ncol0 + cb + hb * 32;  // global output column of r[0]
+            uint32_t r[32];
+            tmem_ld32(t_row + (uint32_t)(cb + hb * 32), r);
+            // residual for this lane's row: issued before the TMEM wait so the two latencies overlap
+            uint4 res[4];
+            if constexpr (kRes) {
 #pragma unroll
-            for (int j4 = 0; j4 < 4; ++j4) {
+              for (int c = 0; c < 4; ++c) {
+                res[c] = make_uint4(0u, 0u, 0u, 0u);
+                if (row_ok && col + 8 * c < p.cout)
+                  res[c] = __ldg(reinterpret_cast<const uint4*>(p.residual + row * p.cout + col + 8 * c));
+              }
+            }
+            tmem_ld_wait();
+            if (cb + hb * 32 + 32 >= p.bn) {  // accumulator fully read: hand it back to the MMA warp early
+              tcgen05_fence_before();
+              mbar_arrive(&tmem_empty[grp]);
+            }
+            f32x2_t v[16];
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
               const float4 b4 = *reinterpret_cast<const float4*>(sbias + col + 4 * j4);  // smem broadcast
-              v[2 * j4] = f2_add(f2_pack(__uint_as_float(r[g][4 * j4]), __uint_as_float(r[g][4 * j4 + 1])),
+              v[2 * j4] = f2_add(f2_pack(__uint_as_float(r[4 * j4]), __uint_as_float(r[4 * j4 + 1])),
                                  f2_pack(b4.x, b4.y));
-              v[2 * j4 + 1] = f2_add(f2_pack(__uint_as_float(r[g][4 * j4 + 2]), __uint_as_float(r[g][4 * j4 + 3])),
+              v[2 * j4 + 1] = f2_add(f2_pack(__uint_as_float(r[4 * j4 + 2]), __uint_as_float(r[4 * j4 + 3])),
                                      f2_pack(b4.z, b4.w));
             }
-            if (p.act == 1) {
+            if constexpr (kAct == 1) {  // SiLU(x) = h + h tanh(h), h = x/2: all MUFUs first, then the FMAs
+              float th[32];
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const f32x2_t h = f2_mul(v[j], half2);
+              for (int j = 0; j < 16; ++j) {
+                v[j] = f2_mul(v[j], half2);
                 float h0, h1;
-                f2_unpack(h, h0, h1);
-                v[j] = f2_fma(h, f2_pack(tanh_fast(h0), tanh_fast(h1)), h);
+                f2_unpack(v[j], h0, h1);
+                th[2 * j] = tanh_fast(h0);
+                th[2 * j + 1] = tanh_fast(h1);
+              }
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = f2_fma(v[j], f2_pack(th[2 * j], th[2 * j + 1]), v[j]);
+            }
+            if constexpr (kRes) {
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                const uint32_t rw[4] = {res[c].x, res[c].y, res[c].z, res[c].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  v[4 * c + j] = f2_add(v[4 * c + j], f2_pack(__uint_as_float(rw[j] << 16),
+                                                              __uint_as_float(rw[j] & 0xffff0000u)));
               }
             }
-            if (p.residual != nullptr && row_ok) {
 #pragma unroll
-              for (int h = 0; h < 2; ++h) {
-                if (col + 8 * h < p.cout) {
-                  const uint4 rr = __ldg(reinterpret_cast<const uint4*>(p.residual + row * p.cout + col + 8 * h));
-                  const uint32_t rw[4] = {rr.x, rr.y, rr.z, rr.w};
-#pragma unroll
-                  for (int j = 0; j < 4; ++j)
-                    v[4 * h + j] = f2_add(v[4 * h + j], f2_pack(__uint_as_float(rw[j] << 16),
-                                                                __uint_as_float(rw[j] & 0xffff0000u)));
-                }
-              }
-            }
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
+            for (int c = 0; c < 4; ++c) {
               uint4 pk;
               float a0, a1;
-              f2_unpack(v[4 * h + 0], a0, a1); pk.x = pack_bf16x2(a0, a1);
-              f2_unpack(v[4 * h + 1], a0, a1); pk.y = pack_bf16x2(a0, a1);
-              f2_unpack(v[4 * h + 2], a0, a1); pk.z = pack_bf16x2(a0, a1);
-              f2_unpack(v[4 * h + 3], a0, a1); pk.w = pack_bf16x2(a0, a1);
-              const int chunk = g * 2 + h;
+              f2_unpack(v[4 * c + 0], a0, a1); pk.x = pack_bf16x2(a0, a1);
+              f2_unpack(v[4 * c + 1], a0, a1); pk.y = pack_bf16x2(a0, a1);
+              f2_unpack(v[4 * c + 2], a0, a1); pk.z = pack_bf16x2(a0, a1);
+              f2_unpack(v[4 * c + 3], a0, a1); pk.w = pack_bf16x2(a0, a1);
+              const int chunk = hb * 4 + c;
               *reinterpret_cast<uint4*>(stg + lane * 128 + ((chunk ^ (lane & 7)) << 4)) = pk;
             }
           }
         }
-        // staging tile -> global: one TMA store of the [32 rows x 64 cols] box (rows >= m and columns >= cout
-        // are clipped by the tensor map; columns past `ncols` only exist when they are >= cout, see choose_bn)
+        // staging tile -> global: one TMA store of the [32 rows x 64 cols] box (rows past the image and columns
+        // >= cout are clipped by the tensor map; columns past `ncols` only exist when they are >= cout, see choose_bn)
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
@@ -412,8 +421,9 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   p.scale_b = (a.gate && a.bn <= 96 && a.bn < (rpi < kBM ? rpi : kBM)) ? 1 : 0;
   p.n_tiles = a.cout_pad / a.bn;
   p.k_chunks = (a.cin + kBK - 1) / kBK;
+  p.acc_stride = (a.bn + 31) / 32 * 32;
   uint32_t cols = 32;
-  while (cols < (uint32_t)(2 * a.bn)) cols <<= 1;
+  while (cols < (uint32_t)(2 * p.acc_stride)) cols <<= 1;
   p.tmem_cols = cols;
   const size_t budget = 220 * 1024;
   int stages = kMaxStages;
@@ -422,33 +432,37 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   p.bias = a.bias;
   p.gate = a.gate;
   p.residual = reinterpret_cast<const bf16*>(a.residual);
-  p.act = a.act;
   const size_t smem = tc_smem_bytes(a.bn, stages);
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
   const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
   const CUtensorMap* ta = reinterpret_cast<const CUtensorMap*>(a.tmap_a);
   const CUtensorMap* tb = reinterpret_cast<const CUtensorMap*>(a.tmap_b);
   const CUtensorMap* to = reinterpret_cast<const CUtensorMap*>(a.tmap_out);
-  cudaError_t e;
-  if (a.gate) {
-    static bool attr_done = false;
-    if (!attr_done) {
-      e = cudaFuncSetAttribute(pwconv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-      if (e != cudaSuccess) return e;
-      attr_done = true;
-    }
-    pwconv_tc_kernel<true><<<grid, 512, smem, s>>>(*ta, *tb, *to, p);
-  } else {
-    static bool attr_done = false;
-    if (!attr_done) {
-      e = cudaFuncSetAttribute(pwconv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-      if (e != cudaSuccess) return e;
-      attr_done = true;
-    }
-    pwconv_tc_kernel<false><<<grid, 384, smem, s>>>(*ta, *tb, *to, p);
+  const bool res = a.residual != nullptr;
+  const int threads = a.gate ? 512 : 384;
+#define TC_LAUNCH(G_, A_, R_)                                                                                  \
+  if ((a.gate != nullptr) == G_ && a.act == A_ && res == R_) {                                                 \
+    static bool attr_done = false;                                                                             \
+    if (!attr_done) {                                                                                          \
+      cudaError_t e = cudaFuncSetAttribute(pwconv_tc_kernel<G_, A_, R_>,                                       \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);           \
+      if (e != cudaSuccess) return e;                                                                          \
+      attr_done = true;                                                                                        \
+    }                                                                                                          \
+    pwconv_tc_kernel<G_, A_, R_><<<grid, threads, smem, s>>>(*ta, *tb, *to, p);                                \
+    count_launch();                                                                                            \
+    return cudaGetLastError();                                                                                 \
   }
-  count_launch();
-  return cudaGetLastError();
+  TC_LAUNCH(false, 1, false)  // expand
+  TC_LAUNCH(false, 0, false)  // conv_head
+  TC_LAUNCH(true, 0, false)   // project
+  TC_LAUNCH(true, 0, true)    // project + skip
+  TC_LAUNCH(false, 0, true)
+  TC_LAUNCH(false, 1, true)
+  TC_LAUNCH(true, 1, false)
+  TC_LAUNCH(true, 1, true)
+#undef TC_LAUNCH
+  return cudaErrorInvalidValue;
 }
 
 }  // namespace b200df
