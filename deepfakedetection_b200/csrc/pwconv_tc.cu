@@ -25,6 +25,8 @@
 #include "kernels.h"
 #include "tc.cuh"
 
+#include <stdlib.h>
+
 #include <mutex>
 
 namespace b200df {
@@ -44,6 +46,9 @@ struct TcParams {
   int rpi;            // rows per image (ungated: m, one "image")
   int tiles_per_img;  // ceil(rpi / 128): M tiles never straddle images
   int acc_stride;     // TMEM columns between the two accumulators (bn rounded up to 32)
+  int b_res;          // scale_b only: the pristine weight matrix (all K chunks) stays resident in shared memory
+  int b_once;         // weights fit one (k chunk, n tile): load the B tile once per ring slot, not per tile
+  int debug;          // B200DF_TC_DEBUG bits (experiments only): 1 = skip the output stores
   int scale_b;        // gated only: 1 = fold the gate into the B (weight) tile, 0 = into the A tile
   int m_tiles, n_tiles, k_chunks, stages;
   uint32_t tmem_cols;
@@ -93,7 +98,8 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int b_bytes = p.bn * kBK * 2;
   const int stage_bytes = kABytes + b_bytes;
-  uint8_t* epi_smem = smem + (size_t)p.stages * stage_bytes;  // 1024-aligned: stage_bytes % 1024 == 0
+  uint8_t* bres = smem + (size_t)p.stages * stage_bytes;      // 1024-aligned: stage_bytes % 1024 == 0
+  uint8_t* epi_smem = bres + (p.b_res ? (size_t)p.k_chunks * b_bytes : 0);
   float* sbias = reinterpret_cast<float*>(epi_smem + 2 * kEpiWarps * kEpiStageBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(sbias + kMaxBiasFloats);
   uint64_t* full_bar = bars;
@@ -101,7 +107,8 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint64_t* scaled_bar = bars + 2 * kMaxStages;
   uint64_t* tmem_full = bars + 3 * kMaxStages;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* bres_bar = tmem_empty + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bres_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = p.m_tiles * p.n_tiles;
@@ -119,6 +126,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       mbar_init(&tmem_full[a], 1);
       mbar_init(&tmem_empty[a], 128);
     }
+    mbar_init(bres_bar, 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -136,15 +144,22 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
+      int it = 0;
+      if (p.b_res) {  // whole weight matrix, once per CTA (148 CTAs re-reading the same few KB per tile
+                      // serialise on one L2 slice)
+        mbar_arrive_expect_tx(bres_bar, (uint32_t)(p.k_chunks * b_bytes));
+        for (int kc = 0; kc < p.k_chunks; ++kc) tma_load_2d(bres + (size_t)kc * b_bytes, &tmap_b, kc * kBK, 0, bres_bar);
+      }
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
         const int img = mt / p.tiles_per_img, lrow0 = (mt - img * p.tiles_per_img) * kBM;
-        for (int kc = 0; kc < p.k_chunks; ++kc) {
+        for (int kc = 0; kc < p.k_chunks; ++kc, ++it) {
           mbar_wait(&empty_bar[s], ph ^ 1);
           uint8_t* sa = smem + (size_t)s * stage_bytes;
-          mbar_arrive_expect_tx(&full_bar[s], (uint32_t)stage_bytes);
+          const bool load_b = !p.b_res && (!p.b_once || it < p.stages);  // b_once: every slot keeps the B tile of its first use
+          mbar_arrive_expect_tx(&full_bar[s], (uint32_t)(load_b ? stage_bytes : kABytes));
           tma_load_3d(sa, &tmap_a, kc * kBK, lrow0, img, &full_bar[s]);
-          tma_load_2d(sa + kABytes, &tmap_b, kc * kBK, nt * p.bn, &full_bar[s]);
+          if (load_b) tma_load_2d(sa + kABytes, &tmap_b, kc * kBK, nt * p.bn, &full_bar[s]);
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
       }
@@ -278,7 +293,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         // >= cout are clipped by the tensor map; columns past `ncols` only exist when they are >= cout, see choose_bn)
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) {
+        if (lane == 0 && !(p.debug & 1)) {
           asm volatile(
               "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
                   reinterpret_cast<uint64_t>(&tmap_out)),
@@ -304,6 +319,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int pc = lc ^ (rg & 7);   // physical chunk ((rg + 16 j) & 7 == rg & 7)
     int s = 0;
     uint32_t ph = 0;
+    if (p.b_res) mbar_wait(bres_bar, 0);
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const int mt = t / p.n_tiles;
       const int img = mt / p.tiles_per_img;
@@ -321,11 +337,13 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         mbar_wait(&full_bar[s], ph);
         if (k_ok) {
           uint8_t* base = smem + (size_t)s * stage_bytes + (p.scale_b ? kABytes : 0) + rg * 128 + (pc << 4);
-          for (int r0 = rg; r0 < nrows; r0 += 64, base += 64 * 128) {
+          // source: the tile itself (scaled in place) or the resident pristine weights
+          const uint8_t* src = p.b_res ? bres + (size_t)kc * b_bytes + rg * 128 + (pc << 4) : base;
+          for (int r0 = rg; r0 < nrows; r0 += 64, base += 64 * 128, src += 64 * 128) {
             uint4 a[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-              if (r0 + 16 * j < nrows) a[j] = *reinterpret_cast<const uint4*>(base + j * 16 * 128);
+              if (r0 + 16 * j < nrows) a[j] = *reinterpret_cast<const uint4*>(src + j * 16 * 128);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               if (r0 + 16 * j < nrows) {
@@ -395,9 +413,9 @@ int encode_tmap_act_bf16(void* tmap_out, const void* base, long long m, int cols
   return encode_tmap_nd_bf16(tmap_out, base, 3, dims, str, box, 128);
 }
 
-static size_t tc_smem_bytes(int bn, int stages) {
-  return 1024 /*align slack*/ + (size_t)stages * (kABytes + bn * kBK * 2) + 2 * kEpiWarps * kEpiStageBytes +
-         kMaxBiasFloats * sizeof(float) + (3 * kMaxStages + 4) * sizeof(uint64_t) + 16;
+static size_t tc_smem_bytes(int bn, int stages, size_t bres_bytes) {
+  return 1024 /*align slack*/ + (size_t)stages * (kABytes + bn * kBK * 2) + bres_bytes +
+         2 * kEpiWarps * kEpiStageBytes + kMaxBiasFloats * sizeof(float) + (3 * kMaxStages + 5) * sizeof(uint64_t) + 16;
 }
 
 cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
@@ -420,19 +438,29 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   // fold the gate into the smaller operand tile: B has bn rows, A has min(128, rpi) valid rows
   p.scale_b = (a.gate && a.bn <= 96 && a.bn < (rpi < kBM ? rpi : kBM)) ? 1 : 0;
   p.n_tiles = a.cout_pad / a.bn;
+  static int dbg = -1;
+  if (dbg < 0) {
+    const char* e = getenv("B200DF_TC_DEBUG");
+    dbg = e ? atoi(e) : 0;
+  }
+  p.debug = dbg;
+  p.b_once = (p.n_tiles == 1 && a.cin <= kBK && !p.scale_b && !(dbg & 2)) ? 1 : 0;
   p.k_chunks = (a.cin + kBK - 1) / kBK;
   p.acc_stride = (a.bn + 31) / 32 * 32;
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * p.acc_stride)) cols <<= 1;
   p.tmem_cols = cols;
   const size_t budget = 220 * 1024;
+  size_t bres_bytes = (size_t)p.k_chunks * a.bn * kBK * 2;
+  p.b_res = (p.scale_b && bres_bytes <= 40 * 1024 && !(dbg & 4)) ? 1 : 0;
+  if (!p.b_res) bres_bytes = 0;
   int stages = kMaxStages;
-  while (stages > 2 && tc_smem_bytes(a.bn, stages) > budget) --stages;
+  while (stages > 2 && tc_smem_bytes(a.bn, stages, bres_bytes) > budget) --stages;
   p.stages = stages;
   p.bias = a.bias;
   p.gate = a.gate;
   p.residual = reinterpret_cast<const bf16*>(a.residual);
-  const size_t smem = tc_smem_bytes(a.bn, stages);
+  const size_t smem = tc_smem_bytes(a.bn, stages, bres_bytes);
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
   const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
   const CUtensorMap* ta = reinterpret_cast<const CUtensorMap*>(a.tmap_a);
