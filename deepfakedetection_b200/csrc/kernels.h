@@ -23,6 +23,13 @@ cudaError_t launch_stem_u8(const uint8_t* x_hwc, int n, int h, int w, const floa
 
 // Pooled sums are Q24 fixed-point int64 (common.cuh: pool_t), accumulated with integer atomics.
 typedef long long pool_t;
+// bf16 output only: implicit GEMM on tcgen05 (stem_tc.cu); launch_stem / launch_stem_u8 dispatch to these
+cudaError_t launch_stem_tc(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias, void* out,
+                           cudaStream_t s);
+cudaError_t launch_stem_tc_u8(const uint8_t* x_hwc, int n, int h, int w, const float* wgt, const float* bias,
+                              float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, void* out,
+                              cudaStream_t s);
+
 cudaError_t launch_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
                           const float* bias, void* out, pool_t* pool, int dtype, cudaStream_t s);
 

@@ -12,6 +12,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <stdlib.h>
+
 namespace b200df {
 
 constexpr int kStemOC = 32;
@@ -89,31 +91,34 @@ stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict_
     const int ow0 = (p - r * pairs_per_row) * 2;
     const int oh = oh0 + r;
     if (oh >= Ho) continue;
-    float acc0[kStemOC], acc1[kStemOC];
+    // packed fp32x2 accumulators (FFMA2: two output channels per issue slot)
+    unsigned long long acc0[kStemOC / 2], acc1[kStemOC / 2];
 #pragma unroll
-    for (int o = 0; o < kStemOC; ++o) { acc0[o] = bs[o]; acc1[o] = bs[o]; }
+    for (int o = 0; o < kStemOC / 2; ++o) {
+      acc0[o] = *reinterpret_cast<const unsigned long long*>(bs + 2 * o);
+      acc1[o] = acc0[o];
+    }
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
 #pragma unroll
       for (int ky = 0; ky < 3; ++ky) {
         const float* prow = patch + (c * PR + 2 * r + ky) * PW + 2 * ow0;
-        float v[5];
+        unsigned long long v[5];
 #pragma unroll
-        for (int i = 0; i < 5; ++i) v[i] = (2 * ow0 + i < PW) ? prow[i] : 0.f;
+        for (int i = 0; i < 5; ++i) {
+          const float t = (2 * ow0 + i < PW) ? prow[i] : 0.f;
+          asm("mov.b64 %0, {%1, %1};" : "=l"(v[i]) : "f"(t));
+        }
 #pragma unroll
         for (int kx = 0; kx < 3; ++kx) {
-          const float4* w4 = reinterpret_cast<const float4*>(ws + ((c * 3 + ky) * 3 + kx) * kStemOC);
+          const ulonglong2* w2 = reinterpret_cast<const ulonglong2*>(ws + ((c * 3 + ky) * 3 + kx) * kStemOC);
 #pragma unroll
           for (int o4 = 0; o4 < kStemOC / 4; ++o4) {
-            float4 w = w4[o4];
-            acc0[4 * o4 + 0] = fmaf(v[kx], w.x, acc0[4 * o4 + 0]);
-            acc0[4 * o4 + 1] = fmaf(v[kx], w.y, acc0[4 * o4 + 1]);
-            acc0[4 * o4 + 2] = fmaf(v[kx], w.z, acc0[4 * o4 + 2]);
-            acc0[4 * o4 + 3] = fmaf(v[kx], w.w, acc0[4 * o4 + 3]);
-            acc1[4 * o4 + 0] = fmaf(v[kx + 2], w.x, acc1[4 * o4 + 0]);
-            acc1[4 * o4 + 1] = fmaf(v[kx + 2], w.y, acc1[4 * o4 + 1]);
-            acc1[4 * o4 + 2] = fmaf(v[kx + 2], w.z, acc1[4 * o4 + 2]);
-            acc1[4 * o4 + 3] = fmaf(v[kx + 2], w.w, acc1[4 * o4 + 3]);
+            const ulonglong2 w = w2[o4];  // 4 consecutive output channels = two fp32 pairs (smem broadcast)
+            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc0[2 * o4]) : "l"(v[kx]), "l"(w.x));
+            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc0[2 * o4 + 1]) : "l"(v[kx]), "l"(w.y));
+            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc1[2 * o4]) : "l"(v[kx + 2]), "l"(w.x));
+            asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc1[2 * o4 + 1]) : "l"(v[kx + 2]), "l"(w.y));
           }
         }
       }
@@ -124,7 +129,12 @@ stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict_
     for (int g = 0; g < kStemOC / 8; ++g) {
       float f[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = silu<kFast>(acc0[8 * g + j]);
+      for (int j = 0; j < 4; ++j) {
+        float lo, hi;
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc0[4 * g + j]));
+        f[2 * j] = silu<kFast>(lo);
+        f[2 * j + 1] = silu<kFast>(hi);
+      }
       store8<TOut>(o0 + 8 * g, f);
     }
     if (ow0 + 1 < Wo) {
@@ -132,7 +142,12 @@ stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict_
       for (int g = 0; g < kStemOC / 8; ++g) {
         float f[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = silu<kFast>(acc1[8 * g + j]);
+        for (int j = 0; j < 4; ++j) {
+          float lo, hi;
+          asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc1[4 * g + j]));
+          f[2 * j] = silu<kFast>(lo);
+          f[2 * j + 1] = silu<kFast>(hi);
+        }
         store8<TOut>(o0 + kStemOC + 8 * g, f);
       }
     }
@@ -158,8 +173,19 @@ static cudaError_t stem_launch(const void* x, int n, int h, int w, const float* 
   return cudaGetLastError();
 }
 
+// debugging aid: B200DF_STEM=simt keeps the CUDA-core stem on the bf16 path
+static bool stem_force_simt() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200DF_STEM");
+    v = (e && e[0] == 's') ? 1 : 0;
+  }
+  return v == 1;
+}
+
 cudaError_t launch_stem(const float* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
                         int dtype, cudaStream_t s) {
+  if (dtype == kBF16 && !stem_force_simt()) return launch_stem_tc(x, n, h, w, wgt, bias, out, s);
   if (dtype == kBF16) return stem_launch<bf16, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
   return stem_launch<float, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
 }
@@ -167,6 +193,8 @@ cudaError_t launch_stem(const float* x, int n, int h, int w, const float* wgt, c
 cudaError_t launch_stem_u8(const uint8_t* x, int n, int h, int w, const float* wgt, const float* bias, float sc0,
                            float sc1, float sc2, float sh0, float sh1, float sh2, void* out, int dtype,
                            cudaStream_t s) {
+  if (dtype == kBF16 && !stem_force_simt())
+    return launch_stem_tc_u8(x, n, h, w, wgt, bias, sc0, sc1, sc2, sh0, sh1, sh2, out, s);
   if (dtype == kBF16) return stem_launch<bf16, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
   return stem_launch<float, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
 }
