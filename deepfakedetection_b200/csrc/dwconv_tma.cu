@@ -24,6 +24,8 @@
 #include "kernels.h"
 #include "tc.cuh"
 
+#include <stdlib.h>
+
 #include <algorithm>
 
 namespace b200df {
@@ -350,6 +352,18 @@ constexpr size_t kDwSmemLimit = 110 * 1024;  // per CTA (2 operand stages + pool
 
 int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
                     const float* bias, void* out, pool_t* pool) {
+  plan.tc = 0;
+  {  // EXPERIMENT, off by default (B200DF_DW_TC=1): stride-1 layers on the tensor cores (dwconv_tc.cu).
+     // Measured 2x SLOWER than this CUDA-core kernel: every tap re-streams the whole pixel tile from shared
+     // memory into the tensor core (k*k tile reads, ~80 cycles per M128 N16 K16 MMA), see DESIGN.md section 4.
+    static int use_tc = -1;
+    if (use_tc < 0) {
+      const char* e = getenv("B200DF_DW_TC");
+      use_tc = (e && e[0] == '1') ? 1 : 0;
+    }
+    if (use_tc && plan_dwconv_tc(plan, x, n, h, w, c, k, stride, wgt, bias, out, pool) == 0) return 0;
+    plan.tc = 0;
+  }
   if (n <= 0 || c % 8 || (k != 3 && k != 5) || (stride != 1 && stride != 2)) return -1;
   if (stride == 2 && (w & 1)) return -1;
   const int pad = (k - 1) / 2;
@@ -439,6 +453,7 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
 }
 
 cudaError_t launch_dwconv_tma(const DwPlan& pl, cudaStream_t s) {
+  if (pl.tc) return launch_dwconv_tc(pl, s);
 #define DW_CASE(K_, S_, TH_) \
   if (pl.k == K_ && pl.stride == S_ && pl.th == TH_) return dw_tma_launch<K_, S_, TH_>(pl, s)
   DW_CASE(3, 1, 8); DW_CASE(3, 1, 7); DW_CASE(3, 2, 8); DW_CASE(3, 2, 7);

@@ -51,10 +51,24 @@ struct DwTmaParams {
   pool_t* pool;          // [n, C] Q24 sums or nullptr
 };
 
+// Tensor-core depthwise kernel (dwconv_tc.cu): stride 1, tiles of 8 x 16 output pixels x 64 channels.
+struct DwTcParams {
+  int C, H, W, n;
+  int tiles_x, tiles_y, ncb, stages;
+  uint32_t box_bytes;
+  int stage_stride;
+  const float* wgt;      // [k*k, C] fp32, BN folded (rounded to bf16 when the diagonal tiles are built)
+  const float* bias;     // [C]
+  pool_t* pool;          // [n, C] Q24 sums or nullptr
+};
+
 // A planned depthwise launch: tensor map + tile geometry for one (layer, n, buffers) combination.
 struct DwPlan {
   alignas(64) unsigned char tmap[128];
+  alignas(64) unsigned char tmap_out[128];  // tensor-core kernel only (TMA store)
   DwTmaParams p;
+  DwTcParams q;
+  int tc = 0;            // 1: planned for the tensor-core kernel
   int k = 0, stride = 0, th = 0;
   int grid = 0, block = 0;
   size_t smem = 0;
@@ -64,6 +78,10 @@ struct DwPlan {
 int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
                     const float* bias, void* out, pool_t* pool);
 cudaError_t launch_dwconv_tma(const DwPlan& plan, cudaStream_t s);
+// Tensor-core variant (stride 1); plan_dwconv_tma tries it first, launch_dwconv_tma dispatches on plan.tc.
+int plan_dwconv_tc(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
+                   const float* bias, void* out, pool_t* pool);
+cudaError_t launch_dwconv_tc(const DwPlan& plan, cudaStream_t s);
 // Generic N-d bf16 tensor map (dims/strides innermost first; strides[0] is implicit).  0 on success.
 int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsigned long long* dims,
                         const unsigned long long* strides_bytes, const unsigned* box, int swizzle);
