@@ -195,6 +195,8 @@ def run_b200(args) -> None:
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"   # NCCL prints its version banner to STDOUT; keep stdout = one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     name = "efficientnet_b0" if args.precision == "bf16" else "efficientnet_b0.b200_fp32"

@@ -37,7 +37,8 @@ constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kABytes = kBM * kBK * 2;  // 16 KB
 constexpr int kMaxStages = 8;
-constexpr int kEpiWarps = 8;              // two groups of four (one group per TMEM accumulator)
+constexpr int kEpiWarps = 8;              // gated kernels: two groups of four (one group per TMEM accumulator)
+constexpr int kEpiWarpsWide = 16;         // ungated kernels (expand, conv_head: wide N, SiLU): two column halves per group
 constexpr int kEpiStageBytes = 32 * 128;  // one staging tile: 32 rows x 64 bf16; TWO per epilogue warp
 constexpr int kMaxBiasFloats = 1536;
 
@@ -114,7 +115,7 @@ struct TileIter {
 };
 
 template <bool kGate, int kAct, bool kRes>
-__global__ void __launch_bounds__(kGate ? 512 : 384, 1)
+__global__ void __launch_bounds__(kGate ? 512 : 640, 1)
 pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_out, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -151,7 +152,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
-      mbar_init(&tmem_empty[a], 128);
+      mbar_init(&tmem_empty[a], kGate ? 128 : 256);
     }
     mbar_init(bres_bar, 1);
     fence_barrier_init();
@@ -223,11 +224,15 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (++s == p.stages) { s = 0; ph ^= 1; }
       }
     }
-  } else if (warp >= 4 && warp < 4 + kEpiWarps) {
-    // ================= epilogue (group = accumulator) =================
-    const int grp = (warp - 4) >> 2;
+  } else if (warp >= 4 && warp < 4 + (kGate ? kEpiWarps : kEpiWarpsWide)) {
+    // ================= epilogue (group = accumulator; ungated: two column-half teams per group) =================
+    constexpr int kHalves = kGate ? 1 : 2;   // teams of 4 warps per accumulator, alternating 64-column blocks
+    constexpr int kBufs = kGate ? 2 : 1;     // staging tiles per warp (64 KB of staging either way)
+    const int ew = warp - 4;
+    const int grp = ew / (4 * kHalves);
+    const int half = (ew >> 2) % kHalves;
     const int q = warp & 3;  // TMEM lane quarter this warp may touch
-    uint8_t* stg_base = epi_smem + (warp - 4) * 2 * kEpiStageBytes;
+    uint8_t* stg_base = epi_smem + ew * kBufs * kEpiStageBytes;
     const f32x2_t half2 = f2_pack(0.5f, 0.5f);
     int stores = 0;  // TMA stores issued by this warp (staging buffer = stores & 1)
     int lt = 0;
@@ -243,11 +248,15 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const size_t row = (size_t)img * p.rpi + lrow0 + lane;         // global row of this lane
       const int ncol0 = nt * p.bn;
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * p.acc_stride);
-      for (int cb = 0; cb < p.bn; cb += 64) {
+      if (half * 64 >= p.bn) {  // this team has no column block in this tile: release the accumulator at once
+        tcgen05_fence_before();
+        mbar_arrive(&tmem_empty[grp]);
+      }
+      for (int cb = half * 64; cb < p.bn; cb += 64 * kHalves) {
         const int ncols = min(64, p.bn - cb);  // multiple of 16
-        uint8_t* stg = stg_base + (stores & 1) * kEpiStageBytes;
-        if (stores >= 2) {  // the store issued two blocks ago must have finished READING this staging tile
-          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        uint8_t* stg = stg_base + (stores % kBufs) * kEpiStageBytes;
+        if (stores >= kBufs) {  // the store that last used this staging tile must have finished READING it
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kBufs - 1) : "memory");
           __syncwarp();
         }
 #pragma unroll
@@ -267,7 +276,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               }
             }
             tmem_ld_wait();
-            if (cb + hb * 32 + 32 >= p.bn) {  // accumulator fully read: hand it back to the MMA warp early
+            if (cb + 64 * kHalves >= p.bn && hb * 32 + 32 >= ncols) {  // this warp's last read of the accumulator
               tcgen05_fence_before();
               mbar_arrive(&tmem_empty[grp]);
             }
@@ -506,7 +515,7 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   const CUtensorMap* tb = reinterpret_cast<const CUtensorMap*>(a.tmap_b);
   const CUtensorMap* to = reinterpret_cast<const CUtensorMap*>(a.tmap_out);
   const bool res = a.residual != nullptr;
-  const int threads = a.gate ? 512 : 384;
+  const int threads = a.gate ? 512 : 640;
 #define TC_LAUNCH(G_, A_, R_)                                                                                  \
   if ((a.gate != nullptr) == G_ && a.act == A_ && res == R_) {                                                 \
     static bool attr_done = false;                                                                             \
