@@ -119,6 +119,30 @@ def synth_state(model, seed: int = 0) -> None:
                 m.bias.copy_(torch.randn(c, generator=g) * 0.1)
 
 
+_CLASS_KERNEL = {"dw": "dwconv", "expand": "pwconv_tc_kernel<0, 1, 0>", "project": "pwconv_tc_kernel<1", "stem": "stem_tc",
+                 "se": "se_kernel", "conv_head": "pwconv_tc_kernel<0, 0, 0>", "head_pool": "head_pool", "classifier": "classifier"}
+
+
+def ncu_traffic_per_launch(cls: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes) of a kernel class, averaged over its
+    launches in the newest committed `ncu --set full` capture of one step (profiles/*_step_metrics.txt)."""
+    files = sorted((ROOT / "profiles").glob("*_step_metrics.txt"))
+    key = _CLASS_KERNEL.get(cls)
+    if not files or key is None:
+        return None, None
+    tot, cnt = 0.0, 0
+    for line in files[-1].read_text().splitlines():
+        if line.startswith("#") or key not in line:
+            continue
+        rest = line.split(key, 1)[1]
+        rest = rest.split(">", 1)[1] if ">" in rest[:12] else rest
+        nums = [t for t in rest.split() if t.replace(".", "", 1).isdigit()]
+        if len(nums) >= 3:
+            tot += float(nums[1]) + float(nums[2])
+            cnt += 1
+    return (tot / cnt * 1e6, files[-1].name) if cnt else (None, None)
+
+
 def peaks() -> tuple[dict, str]:
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -253,9 +277,11 @@ def run_b200(args) -> None:
             hi = sampler.mark()
 
         # ---- timed region 2: host (pinned) inputs through the public module call -> `e2e` ----
-        e2e = None
+        e2e = e2e_u8 = None
         if not args.no_e2e:
             e2e = run_e2e(model, step, B, K, W, dev, rank, world, local)
+            if not cam_mode:
+                e2e_u8 = run_e2e(model, step, B, K, W, dev, rank, world, local, u8=True)
 
         # ---- profiling pass (events around every launch; outside the timed regions) ----
         eng = model._engine
@@ -278,12 +304,12 @@ def run_b200(args) -> None:
         if world > 1:
             dist.destroy_process_group()
         return
-    finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, sampler.summary(lo, hi), model)
+    finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, sampler.summary(lo, hi), model, e2e_u8)
     if world > 1:
         dist.destroy_process_group()
 
 
-def run_e2e(model, step, B, K, W, dev, rank, world, local):
+def run_e2e(model, step, B, K, W, dev, rank, world, local, u8: bool = False):
     """Host-resident fp32 NCHW batches (what the reference's DataLoader hands over, pin_memory=True,
     orchestrator.py:386-395,588): every step copies its batch H2D (copy stream, double-buffered against
     the compute stream, like `.to(device, non_blocking=True)`), runs the module, and reads the packed
@@ -293,8 +319,14 @@ def run_e2e(model, step, B, K, W, dev, rank, world, local):
 
     from deepfakedetection_b200.evaluate import pack_records
 
-    host = [torch.randn(B, 3, 224, 224).pin_memory() for _ in range(2)]
-    dbuf = [torch.empty(B, 3, 224, 224, device=dev) for _ in range(2)]
+    if u8:  # GPU-side input path: uint8 HWC crops, ToTensor + Normalize fused into the stem
+        host = [torch.randint(0, 256, (B, 224, 224, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        dbuf = [torch.empty(B, 224, 224, 3, dtype=torch.uint8, device=dev) for _ in range(2)]
+        step = model.forward_u8
+    else:
+        host = [torch.randn(B, 3, 224, 224).pin_memory() for _ in range(2)]
+        dbuf = [torch.empty(B, 3, 224, 224, device=dev) for _ in range(2)]
+    in_bytes = host[0].numel() * host[0].element_size()
     out_host = torch.empty(K + W, B, 4, dtype=torch.float32).pin_memory()
     copy_s = torch.cuda.Stream(dev)
     comp_s = torch.cuda.current_stream(dev)
@@ -331,13 +363,14 @@ def run_e2e(model, step, B, K, W, dev, rank, world, local):
     ms = float(ms.item())
     assert bool(torch.isfinite(out_host[W:]).all())
     return {"value": round(world * B * K / (ms * 1e-3), 1), "unit": UNIT,
-            "h2d_bytes_per_step": B * 3 * 224 * 224 * 4, "d2h_bytes_per_step": B * 4 * 4,
+            "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": B * 4 * 4,
             "ms_per_step": round(ms / K, 4),
-            "note": "pinned fp32 NCHW host batches, H2D on a copy stream double-buffered with compute; "
-                    "h2d GB/s per GPU = %.1f" % (B * 3 * 224 * 224 * 4 * K / (ms * 1e-3) / 1e9)}
+            "note": ("pinned uint8 HWC host batches (forward_u8)" if u8 else "pinned fp32 NCHW host batches") +
+                    ", H2D on a copy stream double-buffered with compute; h2d GB/s per GPU = %.1f"
+                    % (in_bytes * K / (ms * 1e-3) / 1e9)}
 
 
-def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, clocks, model) -> None:
+def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, clocks, model, e2e_u8=None) -> None:
     import torch
 
     pk, pk_kind = peaks()
@@ -355,8 +388,11 @@ def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, 
     t_launch = t / cnt * 1e-3
     hbm_peak = float(pk["hbm_gbs"])
     achieved = by / cnt / t_launch / 1e9
+    traffic, traffic_src = ncu_traffic_per_launch(dom)
     roofline = {"kernel": dom, "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
-                "frac": round(achieved / hbm_peak, 4), "traffic": None, "peak_source": f"{pk_kind} (MEASURED_PEAKS.json hbm_gbs)",
+                "frac": round(achieved / hbm_peak, 4), "traffic": None if traffic is None else round(traffic),
+                "traffic_source": traffic_src, "algorithmic_bytes_per_launch": round(by / cnt),
+                "peak_source": f"{pk_kind} (MEASURED_PEAKS.json hbm_gbs)",
                 "share_of_step": round(t / reps / prof_ms, 3), "launches_per_step": cnt // reps,
                 "avg_launch_ms": round(t_launch * 1e3, 4)}
     es = 2 if args.precision == "bf16" else 4
@@ -378,6 +414,8 @@ def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, 
     }
     if e2e is not None:
         line["e2e"] = e2e
+    if e2e_u8 is not None:  # extra, not the headline: same metric fed with uint8 crops (4x fewer PCIe bytes)
+        line["e2e_u8"] = e2e_u8
     if not args.no_cpu_baseline and world >= 1:
         steps_cpu = 6
         ips, ms, cores = cpu_eval_images_per_s({k: v.cpu() for k, v in model.state_dict().items()}, 64, steps_cpu, 2)
