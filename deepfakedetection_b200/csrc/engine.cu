@@ -752,6 +752,32 @@ extern "C" int b200df_softmax_pack(const float* logits, const int64_t* labels, i
   return B200DF_OK;
 }
 
+// ---- on-device metrics tail (orchestrator.py:536-546, 605-631) ------------------------------------------------
+extern "C" int b200df_threshold_hist(const float* scores, const int64_t* labels, int n, const double* thresholds,
+                                     int nthr, long long* hist, void* stream) {
+  if (n < 0 || nthr < 1 || !thresholds || !hist || (n > 0 && (!scores || !labels)))
+    return fail(B200DF_E_INVALID, "bad argument");
+  CU_OK(launch_threshold_hist(scores, labels, n, thresholds, nthr, reinterpret_cast<unsigned long long*>(hist),
+                              reinterpret_cast<cudaStream_t>(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_confusion_matrix(const int64_t* targets, const int64_t* preds, int n, int num_classes,
+                                       long long* cm, void* stream) {
+  if (n < 0 || num_classes < 1 || !cm || (n > 0 && (!targets || !preds))) return fail(B200DF_E_INVALID, "bad argument");
+  CU_OK(launch_confusion(targets, preds, n, num_classes, reinterpret_cast<unsigned long long*>(cm),
+                         reinterpret_cast<cudaStream_t>(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_auc_counts(const float* pos_scores, int n_pos, const float* neg_scores_sorted, int n_neg,
+                                 long long* less_equal, void* stream) {
+  if (n_pos < 0 || n_neg < 0 || !less_equal) return fail(B200DF_E_INVALID, "bad argument");
+  CU_OK(launch_auc_count(pos_scores, n_pos, neg_scores_sorted, n_neg, reinterpret_cast<unsigned long long*>(less_equal),
+                         reinterpret_cast<cudaStream_t>(stream)));
+  return B200DF_OK;
+}
+
 // ---- profiling (bench.py's per-kernel roofline; never enabled inside a timed region) ---------------------------
 extern "C" int b200df_set_profile(b200df_handle h, int enable) {
   if (!h) return fail(B200DF_E_INVALID, "NULL handle");

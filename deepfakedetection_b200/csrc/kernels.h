@@ -140,4 +140,12 @@ cudaError_t launch_head_backward(const float* a_nchw, const float* grad_logits, 
 cudaError_t launch_softmax_pack(const float* logits, const int64_t* labels, int n, int num_classes, float* packed,
                                 cudaStream_t s);
 
+// on-device metrics tail (metrics.cu)
+cudaError_t launch_threshold_hist(const float* scores, const int64_t* labels, int n, const double* thr, int nthr,
+                                  unsigned long long* hist, cudaStream_t s);
+cudaError_t launch_confusion(const int64_t* targets, const int64_t* preds, int n, int nc, unsigned long long* cm,
+                             cudaStream_t s);
+cudaError_t launch_auc_count(const float* pos, int np, const float* neg_sorted, int nn, unsigned long long* out,
+                             cudaStream_t s);
+
 }  // namespace b200df

@@ -106,6 +106,106 @@ def best_threshold(scores: np.ndarray, truth: np.ndarray) -> float:
     return float(thr[int(np.argmax(bal))])  # first maximum, like the reference's strict `>`
 
 
+# ---- on-device metrics tail ---------------------------------------------------------
+def threshold_from_hist(hist: np.ndarray, thresholds: np.ndarray) -> float:
+    """Histograms of `b200df_threshold_hist` -> the reference's best threshold (orchestrator.py:536-546).
+
+    hist[c, j] = number of class-c samples whose score is >= exactly j thresholds.  For threshold k the
+    predicted positives are the samples with j > k, so TP/FP are suffix sums; balanced accuracy is
+    sklearn's mean of per-class recalls in float64; the first strict maximum wins, like the reference loop.
+    Pure host arithmetic on 2 x 502 integers (testable without a GPU)."""
+    hist = np.asarray(hist, dtype=np.int64).reshape(2, -1)
+    nthr = hist.shape[1] - 1
+    n_neg, n_pos = int(hist[0].sum()), int(hist[1].sum())
+    if n_neg == 0 or n_pos == 0:
+        return 0.5  # the reference skips the sweep when only one class is present
+    suffix = np.cumsum(hist[:, ::-1], axis=1)[:, ::-1]      # suffix[c, j] = sum_{i >= j} hist[c, i]
+    best_bal, chosen = -1.0, 0.5
+    for k in range(nthr):
+        tp = int(suffix[1, k + 1])
+        fp = int(suffix[0, k + 1])
+        recalls = np.array([(n_neg - fp) / n_neg, tp / n_pos], dtype=np.float64)
+        bal = float(np.mean(recalls))
+        if bal > best_bal:
+            best_bal, chosen = bal, float(thresholds[k])
+    return chosen
+
+
+def best_threshold_device(scores: torch.Tensor, labels: torch.Tensor) -> float:
+    """The 501-point sweep with the O(N) part on the GPU: scores float32 [n] (probs[:, 1]), labels int64 [n]."""
+    from . import _lib
+    from .engine import _ptr, _stream_ptr
+
+    thr = np.linspace(0.0, 1.0, 501, dtype=np.float64)
+    n = scores.shape[0]
+    if n == 0:
+        return 0.5
+    dev = scores.device
+    scores = scores.contiguous().float()
+    labels = labels.to(device=dev, dtype=torch.int64).contiguous()
+    thr_d = torch.from_numpy(thr).to(dev)
+    hist = torch.zeros(2 * (thr.size + 1), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().b200df_threshold_hist(_ptr(scores), _ptr(labels), n, _ptr(thr_d), thr.size, _ptr(hist),
+                                                    _stream_ptr(dev)))
+    return threshold_from_hist(hist.cpu().numpy(), thr)
+
+
+def confusion_matrix_device(targets: torch.Tensor, preds: torch.Tensor, num_classes: int) -> np.ndarray:
+    """counts[target, pred] (sklearn.metrics.confusion_matrix with labels 0..C-1) on the GPU."""
+    from . import _lib
+    from .engine import _ptr, _stream_ptr
+
+    dev = targets.device
+    cm = torch.zeros((num_classes, num_classes), dtype=torch.int64, device=dev)
+    n = targets.shape[0]
+    if n:
+        t = targets.to(torch.int64).contiguous()
+        p = preds.to(device=dev, dtype=torch.int64).contiguous()
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().b200df_confusion_matrix(_ptr(t), _ptr(p), n, num_classes, _ptr(cm), _stream_ptr(dev)))
+    return cm.cpu().numpy()
+
+
+def roc_auc_device(targets: torch.Tensor, scores: torch.Tensor) -> float:
+    """Binary ROC-AUC = P(score_pos > score_neg) + P(equal)/2 (what roc_auc_score's trapezoid integrates to).
+    torch.sort orders the negatives (plumbing); the pair counting is `b200df_auc_counts`."""
+    from . import _lib
+    from .engine import _ptr, _stream_ptr
+
+    dev = scores.device
+    scores = scores.contiguous().float()
+    pos = scores[targets == 1].contiguous()
+    neg = torch.sort(scores[targets != 1]).values.contiguous()
+    if pos.numel() == 0 or neg.numel() == 0:
+        raise ValueError("Only one class present in y_true. ROC AUC score is not defined in that case.")
+    out = torch.zeros(2, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().b200df_auc_counts(_ptr(pos), pos.numel(), _ptr(neg), neg.numel(), _ptr(out), _stream_ptr(dev)))
+    less, equal = (int(v) for v in out.cpu())
+    return (less + 0.5 * equal) / (pos.numel() * neg.numel())
+
+
+def compute_metrics_device(records: torch.Tensor, num_classes: int, threshold: float | None = None) -> dict[str, Any]:
+    """`compute_metrics` (orchestrator.py:605-635) on the gathered device records [n, C+2] without the O(N)
+    host work: only the confusion matrix / AUC counts cross PCIe."""
+    c = records.shape[1] - 2
+    probs = records[:, :c]
+    preds = records[:, c].round().long()
+    targets = records[:, c + 1].round().long()
+    if num_classes == 2 and threshold is not None:
+        preds = (probs[:, 1] >= threshold).long()   # the reference's own expression (orchestrator.py:609)
+    cm = confusion_matrix_device(targets, preds, num_classes)
+    n = int(cm.sum())
+    out: dict[str, Any] = {"accuracy": float(np.float32(np.trace(cm)) / np.float32(n)) if n else float("nan")}
+    if (cm.sum(1) > 0).sum() > 1 and num_classes == 2:
+        out["roc_auc"] = roc_auc_device(targets, probs[:, 1])
+    if num_classes == 2 and threshold is not None:
+        out["threshold"] = float(threshold)
+    out["confusion_matrix"] = cm.tolist()
+    return out
+
+
 @torch.inference_mode()
 def evaluate_sharded(model, images: torch.Tensor, labels: torch.Tensor, batch_size: int = 256, group=None,
                      threshold: float | None = None) -> dict[str, Any]:

@@ -120,6 +120,22 @@ int b200df_head_backward(b200df_handle h, const float* a_nchw, const float* grad
 int b200df_softmax_pack(const float* logits, const int64_t* labels, int n, int num_classes,
                         float* packed, void* stream);
 
+/* ---- on-device metrics tail (the counting work behind orchestrator.py:536-546 and :605-631) ---- */
+/* Threshold sweep: hist[cls*(nthr+1) + j] += #{samples of class cls (label==1 -> 1, else 0) whose float32
+ * score, promoted to double, is >= exactly j of the ascending `thresholds`} -- so for threshold k,
+ * TP_k = sum_{j>k} hist[1][j], FP_k = sum_{j>k} hist[0][j] (same `score >= thr` decisions as the reference's
+ * 501 balanced_accuracy_score calls).  hist: int64 [2*(nthr+1)] device, zeroed by the caller; nthr <= 1024. */
+int b200df_threshold_hist(const float* scores, const int64_t* labels, int n, const double* thresholds,
+                          int nthr, long long* hist, void* stream);
+/* cm[t*num_classes + p] += 1 for every (target t, prediction p); int64 device, zeroed by the caller
+ * (sklearn.metrics.confusion_matrix, orchestrator.py:631). */
+int b200df_confusion_matrix(const int64_t* targets, const int64_t* preds, int n, int num_classes,
+                            long long* cm, void* stream);
+/* ROC-AUC counts (roc_auc_score, orchestrator.py:619-622): less_equal[0] += #{(p,q): neg[q] < pos[p]},
+ * less_equal[1] += #{(p,q): neg[q] == pos[p]}; neg_scores_sorted ascending.  AUC = (less + equal/2)/(P*N). */
+int b200df_auc_counts(const float* pos_scores, int n_pos, const float* neg_scores_sorted, int n_neg,
+                      long long* less_equal, void* stream);
+
 /* Count of kernel launches issued by this library on the calling thread since the last
  * reset (bench.py reports it as gpu_launches). */
 long long b200df_launch_count(void);

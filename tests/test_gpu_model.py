@@ -262,3 +262,42 @@ def test_sharded_evaluation_single_rank(model_bf16, batch):
     res = evaluate_sharded(model_bf16, x, labels, batch_size=24)
     assert res["probs"].shape == (64, 2) and res["accuracy"] >= 0.95
     assert np.array(res["confusion_matrix"]).sum() == 64
+
+
+@pytest.mark.parametrize("case", ["random", "ties", "skewed"])
+def test_device_metrics_tail_matches_sklearn(case):
+    """threshold sweep / confusion matrix / ROC-AUC counted on the GPU vs the reference's sklearn calls."""
+    import warnings
+
+    from sklearn.metrics import confusion_matrix, roc_auc_score
+
+    from deepfakedetection_b200.evaluate import (best_threshold_device, compute_metrics, compute_metrics_device,
+                                                 confusion_matrix_device, roc_auc_device)
+    from test_host import _reference_threshold_loop
+
+    rng = np.random.default_rng({"random": 5, "ties": 6, "skewed": 7}[case])
+    n = 5000
+    truth = (rng.random(n) < (0.05 if case == "skewed" else 0.5)).astype(np.int64)
+    p1 = np.clip(rng.normal(0.35 + 0.3 * truth, 0.25), 0, 1).astype(np.float32)
+    if case == "ties":
+        p1 = (np.round(p1 * 50) / 50).astype(np.float32)
+    scores, labels = torch.from_numpy(p1).cuda(), torch.from_numpy(truth).cuda()
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        want_thr = _reference_threshold_loop(p1, truth)
+    thr = best_threshold_device(scores, labels)
+    assert thr == want_thr
+    preds = (scores >= thr).long()
+    np.testing.assert_array_equal(confusion_matrix_device(labels, preds, 2), confusion_matrix(truth, preds.cpu().numpy()))
+    assert abs(roc_auc_device(labels, scores) - roc_auc_score(truth, p1)) < 1e-12
+    # the whole block, from packed records, against compute_metrics (sklearn on the host)
+    probs = torch.stack([1 - scores, scores], 1)
+    rec = torch.cat([probs, probs.argmax(1, keepdim=True).float(), labels[:, None].float()], 1)
+    got = compute_metrics_device(rec, 2, threshold=thr)
+    want = compute_metrics(probs.cpu(), probs.argmax(1).cpu(), labels.cpu(), 2, threshold=thr)
+    assert got["confusion_matrix"] == want["confusion_matrix"] and got["accuracy"] == want["accuracy"]
+    assert abs(got["roc_auc"] - want["roc_auc"]) < 1e-12 and got["threshold"] == want["threshold"]
+    # multi-class confusion matrix
+    t5 = torch.randint(0, 5, (3000,), device="cuda")
+    p5 = torch.randint(0, 5, (3000,), device="cuda")
+    np.testing.assert_array_equal(confusion_matrix_device(t5, p5, 5), confusion_matrix(t5.cpu().numpy(), p5.cpu().numpy(), labels=list(range(5))))

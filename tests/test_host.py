@@ -163,3 +163,55 @@ def test_show_cam_on_image_and_target():
     with pytest.raises(ValueError):
         show_cam_on_image(img * 3, mask)
     assert float(ClassifierOutputTarget(1)(torch.tensor([[1.0, 2.0]]))) == 2.0
+
+
+def _reference_threshold_loop(scores, truth):
+    """orchestrator.py:536-546 verbatim (sklearn in the loop)."""
+    import numpy as np
+    from sklearn.metrics import balanced_accuracy_score
+
+    thresholds = np.linspace(0.0, 1.0, 501, dtype=np.float64)
+    best_bal, chosen = -1.0, 0.5
+    for thr in thresholds:
+        preds = (scores >= thr).astype(np.int64)
+        bal = balanced_accuracy_score(truth, preds)
+        if bal > best_bal:
+            best_bal, chosen = float(bal), float(thr)
+    return float(chosen)
+
+
+def _hist_like_kernel(scores, truth, thr):
+    import numpy as np
+
+    j = (scores.astype(np.float64)[:, None] >= thr[None, :]).sum(1)   # thresholds ascending -> prefix property
+    hist = np.zeros((2, thr.size + 1), dtype=np.int64)
+    for c in (0, 1):
+        np.add.at(hist[c], j[(truth == 1) == bool(c)], 1)
+    return hist
+
+
+@pytest.mark.parametrize("case", ["random", "ties", "separable", "skewed"])
+def test_threshold_from_hist_matches_reference_sweep(case):
+    """Host half of the on-device threshold sweep: histograms -> same threshold as 501 sklearn calls."""
+    import warnings
+
+    import numpy as np
+
+    from deepfakedetection_b200.evaluate import best_threshold, threshold_from_hist
+
+    rng = np.random.default_rng({"random": 1, "ties": 2, "separable": 3, "skewed": 4}[case])
+    n = 700
+    truth = (rng.random(n) < (0.1 if case == "skewed" else 0.5)).astype(np.int64)
+    scores = rng.random(n).astype(np.float32)
+    if case == "ties":
+        scores = (np.round(scores * 20) / 20).astype(np.float32)     # many scores exactly on thresholds
+    if case == "separable":
+        scores = np.where(truth == 1, 0.7 + 0.3 * scores, 0.3 * scores).astype(np.float32)
+    thr = np.linspace(0.0, 1.0, 501, dtype=np.float64)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        want = _reference_threshold_loop(scores, truth)
+    assert threshold_from_hist(_hist_like_kernel(scores, truth, thr), thr) == want
+    assert best_threshold(scores, truth) == want
+    # one class only: the reference skips the sweep and keeps 0.5
+    assert threshold_from_hist(_hist_like_kernel(scores, np.zeros(n, dtype=np.int64), thr), thr) == 0.5
