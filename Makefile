@@ -17,7 +17,14 @@ all: $(OUT)
 $(OUT): $(OBJS)
 	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -cudart static -o $@ $(OBJS)
 
-clean:
-	rm -f $(OBJS) $(SRC_DIR)/*.ptxas.log $(OUT)
+# dev build with per-role wait-cycle counters in the tcgen05 GEMM (tools/tc_prof.py)
+PROF_OUT := deepfakedetection_b200/libb200df_prof.so
+prof: $(OBJS)
+	$(NVCC) $(NVFLAGS) -DTC_PROF -c $(SRC_DIR)/pwconv_tc.cu -o $(SRC_DIR)/pwconv_tc_prof.o
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -cudart static -o $(PROF_OUT) \
+	    $(filter-out $(SRC_DIR)/pwconv_tc.o,$(OBJS)) $(SRC_DIR)/pwconv_tc_prof.o
 
-.PHONY: all clean
+clean:
+	rm -f $(OBJS) $(SRC_DIR)/*.ptxas.log $(SRC_DIR)/pwconv_tc_prof.o $(OUT) $(PROF_OUT)
+
+.PHONY: all clean prof

@@ -8,8 +8,8 @@
 // Every one of these GEMMs except conv_head is HBM/L2-bound with a tiny K x N, so the kernel is a
 // streaming pipeline whose cost is the EPILOGUE, not the MMA:
 //   * persistent CTAs, static round-robin over (m_tile, n_tile) tiles of 128 x BN;
-//   * warp 0: TMA producer -- A tile [128 x 64] and B tile [BN x 64] per K chunk, 128B swizzle,
-//     multi-stage mbarrier ring; K / M / N tails are zero-filled by TMA out-of-bounds handling;
+//   * warps 0, 2, 3: TMA producers (tiles dealt round-robin) -- A tile [128 x 64] and B tile [BN x 64] per
+//     K chunk, 128B swizzle, multi-stage mbarrier ring; K / M / N tails zero-filled by TMA OOB handling;
 //   * warp 1: one lane issues tcgen05.mma (M=128, N=BN, K=16) into a double-buffered TMEM
 //     accumulator and commits to the ring's `empty` barriers and to `tmem_full`;
 //   * warps 4-7 and 8-11: TWO epilogue groups, one per TMEM accumulator, alternating tiles --
@@ -25,6 +25,7 @@
 #include "kernels.h"
 #include "tc.cuh"
 
+#include <stdio.h>
 #include <stdlib.h>
 
 #include <mutex>
@@ -48,6 +49,8 @@ struct TcParams {
   int tiles_per_img;  // ceil(rpi / 128): M tiles never straddle images
   int acc_stride;     // TMEM columns between the two accumulators (bn rounded up to 32)
   int b_res;          // scale_b only: the pristine weight matrix (all K chunks) stays resident in shared memory
+  int prof_slot;      // TC_PROF builds: row of g_tc_prof this launch writes
+  int np;             // TMA producer lanes (1..3); stages % np == 0
   int b_once;         // weights fit one (k chunk, n tile): load the B tile once per ring slot, not per tile
   int debug;          // B200DF_TC_DEBUG bits (experiments only): 1 = skip the output stores
   int scale_b;        // gated only: 1 = fold the gate into the B (weight) tile, 0 = into the A tile
@@ -92,6 +95,29 @@ __device__ __forceinline__ uint32_t scale_bf16x2(uint32_t a, float g0, float g1)
 
 // (n tile, M sub-tile, image) of a CTA's current tile, advanced by the grid stride in mixed radix: every role
 // is a lone warp per scheduler (~0.2 IPC), so the per-tile bookkeeping has no divisions.
+// Role-level timing (dev builds only: `make EXTRA=-DTC_PROF`): lane 0 of one warp per role accumulates the
+// cycles it spends inside each mbarrier wait; tools/tc_prof.py prints the table.
+#ifdef TC_PROF
+constexpr int kProfLaunches = 64;
+__device__ unsigned long long g_tc_prof[kProfLaunches * 148 * 32];
+#define PROF_DECL unsigned long long prof_w[7] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull}; const long long prof_t0 = clock64();
+#define PROF_WAIT(i, ...) { const long long prof_c0 = clock64(); __VA_ARGS__; prof_w[i] += (unsigned long long)(clock64() - prof_c0); }
+#define PROF_BEGIN long long prof_b0 = clock64();
+#define PROF_LAP(i) { const long long prof_b1 = clock64(); prof_w[i] += (unsigned long long)(prof_b1 - prof_b0); prof_b0 = prof_b1; }
+#define PROF_END(role)                                                                          \
+  if (lane == 0) {                                                                              \
+    unsigned long long* g = g_tc_prof + ((size_t)p.prof_slot * 148 + blockIdx.x) * 32 + (role) * 8; \
+    g[0] = (unsigned long long)(clock64() - prof_t0);                                           \
+    for (int i_ = 0; i_ < 7; ++i_) g[1 + i_] = prof_w[i_];                                       \
+  }
+#else
+#define PROF_DECL
+#define PROF_WAIT(i, ...) { __VA_ARGS__; }
+#define PROF_BEGIN
+#define PROF_LAP(i)
+#define PROF_END(role)
+#endif
+
 struct TileIter {
   int nt, sub, img, d_nt, d_sub, d_img, n_tiles, tiles_per_img;
   __device__ __forceinline__ TileIter(int t0, int step, int n_tiles_, int tiles_per_img_)
@@ -126,7 +152,8 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint8_t* bres = smem + (size_t)p.stages * stage_bytes;      // 1024-aligned: stage_bytes % 1024 == 0
   uint8_t* epi_smem = bres + (p.b_res ? (size_t)p.k_chunks * b_bytes : 0);
   float* sbias = reinterpret_cast<float*>(epi_smem + 2 * kEpiWarps * kEpiStageBytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sbias + kMaxBiasFloats);
+  float* sgate = sbias + kMaxBiasFloats;  // [stages][64] fp32: the SE gate slice of every ring slot's (image, K chunk)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sgate + kMaxStages * kBK);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kMaxStages;
   uint64_t* scaled_bar = bars + 2 * kMaxStages;
@@ -135,7 +162,8 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint64_t* bres_bar = tmem_empty + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bres_bar + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: tells ptxas it is warp-uniform, so the role loops run on uniform registers
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int num_tiles = p.m_tiles * p.n_tiles;
   // static round-robin tile order: at any moment the 148 CTAs stream through one contiguous window of the
   // activation tensor (DRAM-page friendly; measured faster than a contiguous range per CTA)
@@ -148,7 +176,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
-      mbar_init(&scaled_bar[s], 128);
+      mbar_init(&scaled_bar[s], 4);  // one arrival per scaler warp
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
@@ -165,65 +193,98 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_ptr, 0);
 
-  if (warp == 0) {
-    // ================= TMA producer =================
-    if (lane == 0) {
-      int s = 0;
-      uint32_t ph = 0;
-      int it = 0;
-      if (p.b_res) {  // whole weight matrix, once per CTA (148 CTAs re-reading the same few KB per tile
-                      // serialise on one L2 slice)
+  if (warp == 0 || warp == 2 || warp == 3) {
+    // ================= TMA producers (up to three warps, one lane each) =================
+    // A lone lane needs ~1000 cycles of dependent uniform-datapath instructions per TMA issue (measured: the
+    // single producer never waited on an `empty` barrier -- it WAS the critical path of the thin layers), so
+    // the flattened (tile, K chunk) sequence is dealt round-robin to p.np producer lanes.  p.stages is a
+    // multiple of p.np, hence every ring slot has exactly ONE producer and the parity waits stay unambiguous
+    // (a producer two ring revolutions ahead of another on the same slot would alias mbarrier phases).
+    const int pw = warp == 0 ? 0 : warp - 1;
+    if (pw < p.np) {
+      if (p.b_res && pw == 0 && elect_one()) {  // whole weight matrix, once per CTA (148 CTAs re-reading the
+                                                // same few KB per tile serialise on one L2 slice)
         mbar_arrive_expect_tx(bres_bar, (uint32_t)(p.k_chunks * b_bytes));
         for (int kc = 0; kc < p.k_chunks; ++kc) tma_load_2d(bres + (size_t)kc * b_bytes, &tmap_b, kc * kBK, 0, bres_bar);
       }
+      __syncwarp();
+      PROF_DECL
+      int it = pw;               // flattened (tile, K chunk) index of this producer's next load
+      int s = pw;                // = it % stages (pw < np <= stages)
+      uint32_t ph = 0;
+      int kc = pw, t = t_begin;
       TileIter ti(t_begin, t_step, p.n_tiles, p.tiles_per_img);
-      for (int t = t_begin; t < t_end; t += t_step, ti.next()) {
-        const int nt = ti.nt, img = ti.img, lrow0 = ti.sub * kBM;
-        for (int kc = 0; kc < p.k_chunks; ++kc, ++it) {
-          mbar_wait(&empty_bar[s], ph ^ 1);
-          uint8_t* sa = smem + (size_t)s * stage_bytes;
-          const bool load_b = !p.b_res && (!p.b_once || it < p.stages);  // b_once: every slot keeps the B tile of its first use
-          mbar_arrive_expect_tx(&full_bar[s], (uint32_t)(load_b ? stage_bytes : kABytes));
-          tma_load_3d(sa, &tmap_a, kc * kBK, lrow0, img, &full_bar[s]);
-          if (load_b) tma_load_2d(sa + kABytes, &tmap_b, kc * kBK, nt * p.bn, &full_bar[s]);
-          if (++s == p.stages) { s = 0; ph ^= 1; }
+      while (kc >= p.k_chunks) { kc -= p.k_chunks; t += t_step; ti.next(); }
+      while (t < t_end) {
+        PROF_WAIT(0, mbar_wait(&empty_bar[s], ph ^ 1))
+        uint8_t* sa = smem + (size_t)s * stage_bytes;
+        const bool load_b = !p.b_res && (!p.b_once || it < p.stages);  // b_once: every slot keeps the B tile of its first use
+        const int c_k = kc * kBK, c_row = ti.sub * kBM, c_img = ti.img, c_n = ti.nt * p.bn;
+        // gated: the image's gate slice for this K chunk rides the same barrier (the scaler warps then read it
+        // from shared memory instead of stalling on an L2 round trip per chunk)
+        const uint32_t g_bytes = kGate ? (uint32_t)min(kBK, p.cin - c_k) * 4u : 0u;
+        const uint32_t tx_bytes = (uint32_t)(load_b ? stage_bytes : kABytes) + g_bytes;
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&full_bar[s], tx_bytes);
+          tma_load_3d(sa, &tmap_a, c_k, c_row, c_img, &full_bar[s]);
+          if constexpr (kGate) bulk_load_1d(sgate + s * kBK, p.gate + (size_t)c_img * p.cin + c_k, g_bytes, &full_bar[s]);
+          if (load_b) tma_load_2d(sa + kABytes, &tmap_b, c_k, c_n, &full_bar[s]);
         }
+        __syncwarp();
+        it += p.np;
+        s += p.np;
+        if (s >= p.stages) { s -= p.stages; ph ^= 1; }
+        kc += p.np;
+        while (kc >= p.k_chunks) { kc -= p.k_chunks; t += t_step; ti.next(); }
       }
+      if (pw == 0) { PROF_END(0) }
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
     const uint32_t idesc = make_idesc_bf16_m128((uint32_t)p.bn);
+    const uint64_t desc0 = make_sw128_kmajor_desc(smem_u32(smem));  // A tile of ring slot 0
+    const int stage16 = stage_bytes >> 4;
     int s = 0;
     uint32_t ph = 0;
     int lt = 0;
+    PROF_DECL
     for (int t = t_begin; t < t_end; t += t_step, ++lt) {
       const int acc = lt & 1;
       const uint32_t acc_ph = (lt >> 1) & 1;
-      mbar_wait(&tmem_empty[acc], acc_ph ^ 1);
+      PROF_WAIT(0, mbar_wait(&tmem_empty[acc], acc_ph ^ 1))
       tcgen05_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride);
       for (int kc = 0; kc < p.k_chunks; ++kc) {
-        mbar_wait(kGate ? &scaled_bar[s] : &full_bar[s], ph);
+        PROF_WAIT(1, mbar_wait(kGate ? &scaled_bar[s] : &full_bar[s], ph))
         tcgen05_fence_after();
-        if (lane == 0) {
-          const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
-          const uint64_t da = make_sw128_kmajor_desc(a_addr);
-          const uint64_t db = make_sw128_kmajor_desc(a_addr + kABytes);
-          int krem = p.cin - kc * kBK;
-          int nk = krem >= kBK ? kBK / 16 : (krem + 15) / 16;
-          for (int k = 0; k < nk; ++k) {
-            // +32 bytes per K=16 step inside the swizzle atom -> +2 in the (addr >> 4) field
-            umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kc | k) ? 1u : 0u);
+        PROF_BEGIN
+        const uint64_t da = desc0 + (uint64_t)(uint32_t)(s * stage16);  // (addr >> 4) field; smem < 256 KB: no carry
+        const uint64_t db = da + (uint64_t)(kABytes >> 4);
+        const int krem = p.cin - kc * kBK;
+        const uint32_t acc0 = kc ? 1u : 0u;
+        if (elect_one()) {
+          // +32 bytes per K=16 step inside the swizzle atom -> +2 in the (addr >> 4) field
+          if (krem >= kBK) {
+            umma_bf16(d_tmem, da, db, idesc, acc0);
+            umma_bf16(d_tmem, da + 2ull, db + 2ull, idesc, 1u);
+            umma_bf16(d_tmem, da + 4ull, db + 4ull, idesc, 1u);
+            umma_bf16(d_tmem, da + 6ull, db + 6ull, idesc, 1u);
+          } else {
+            const int nk = (krem + 15) >> 4;
+            for (int k = 0; k < nk; ++k)
+              umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kc | k) ? 1u : 0u);
           }
           umma_commit(&empty_bar[s]);
           if (kc == p.k_chunks - 1) umma_commit(&tmem_full[acc]);
         }
         __syncwarp();
+        PROF_LAP(2)
         if (++s == p.stages) { s = 0; ph ^= 1; }
       }
     }
+    PROF_END(1)
   } else if (warp >= 4 && warp < 4 + (kGate ? kEpiWarps : kEpiWarpsWide)) {
     // ================= epilogue (group = accumulator; ungated: two column-half teams per group) =================
     constexpr int kHalves = kGate ? 1 : 2;   // teams of 4 warps per accumulator, alternating 64-column blocks
@@ -236,12 +297,13 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const f32x2_t half2 = f2_pack(0.5f, 0.5f);
     int stores = 0;  // TMA stores issued by this warp (staging buffer = stores & 1)
     int lt = 0;
+    PROF_DECL
     // this group's tiles: every second tile of the CTA, starting at t_begin + grp * t_step
     TileIter ti(t_begin + grp * t_step, 2 * t_step, p.n_tiles, p.tiles_per_img);
     for (int t = t_begin + grp * t_step; t < t_end; t += 2 * t_step, lt += 2, ti.next()) {
       const int nt = ti.nt, img = ti.img;
       const uint32_t acc_ph = (lt >> 1) & 1;
-      mbar_wait(&tmem_full[grp], acc_ph);
+      PROF_WAIT(0, mbar_wait(&tmem_full[grp], acc_ph))
       tcgen05_fence_after();
       const int lrow0 = ti.sub * kBM + q * 32;  // first row of this warp inside the image
       const bool row_ok = lrow0 + lane < p.rpi;
@@ -256,8 +318,8 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int ncols = min(64, p.bn - cb);  // multiple of 16
         uint8_t* stg = stg_base + (stores % kBufs) * kEpiStageBytes;
         if (stores >= kBufs) {  // the store that last used this staging tile must have finished READING it
-          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kBufs - 1) : "memory");
-          __syncwarp();
+          PROF_WAIT(1, if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kBufs - 1) : "memory");
+                    __syncwarp())
         }
 #pragma unroll
         for (int hb = 0; hb < 2; ++hb) {  // two 32-column halves of the 64-column staging tile
@@ -275,7 +337,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                   res[c] = __ldg(reinterpret_cast<const uint4*>(p.residual + row * p.cout + col + 8 * c));
               }
             }
-            tmem_ld_wait();
+            PROF_WAIT(2, tmem_ld_wait())
             if (cb + 64 * kHalves >= p.bn && hb * 32 + 32 >= ncols) {  // this warp's last read of the accumulator
               tcgen05_fence_before();
               mbar_arrive(&tmem_empty[grp]);
@@ -340,6 +402,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         ++stores;
       }
     }
+    if (ew == 0) { PROF_END(2) }
     if (stores > 0 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   } else if (kGate && warp >= 4 + kEpiWarps) {
     // ================= SE-gate scaler =================
@@ -347,42 +410,31 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // into whichever operand tile is smaller:  sum_k (a_k g_k) w_k  ==  sum_k a_k (g_k w_k).
     //   scale_b: B tile [BN x 64] (weights) *= gate   -- the big-spatial layers, BN = 16..96 rows
     //   else   : A tile [rows x 64] (activations) *= gate -- only the image's valid rows
-    // A thread owns ONE 16-byte K chunk (8 channels): its 8 fp32 gate values are fetched BEFORE the wait on
-    // the TMA barrier and stay in registers for all of its rows (rows ts/8, ts/8 + 16, ...).
+    // A thread owns ONE 16-byte K chunk (8 channels): its 8 fp32 gate values come from the ring slot's gate
+    // slice (bulk-copied by the producer on the same barrier as the tile) and stay in registers for all of
+    // its rows (rows ts/8, ts/8 + 16, ...).
     const int ts = threadIdx.x - 32 * (4 + kEpiWarps);
     const int lc = ts & 7;          // logical 16-B chunk inside the 128-B swizzled row
     const int rg = ts >> 3;         // first row; rows rg + 16 j
     const int pc = lc ^ (rg & 7);   // physical chunk ((rg + 16 j) & 7 == rg & 7)
     int s = 0;
     uint32_t ph = 0;
-    if (p.b_res) mbar_wait(bres_bar, 0);
+    PROF_DECL
+    PROF_WAIT(1, if (p.b_res) mbar_wait(bres_bar, 0))
     // (n tile, M sub-tile, image) of the current tile, advanced by the grid stride in mixed radix: a lone warp
     // per scheduler runs at ~0.2 IPC, so there are no divisions and as few instructions as possible per tile
     TileIter ti(t_begin, t_step, p.n_tiles, p.tiles_per_img);
     const int kq_max = p.cin >> 3;
-    // this thread's gate values for (image, K chunk), fetched one iteration AHEAD (L2 latency)
-    auto fetch_gate = [&](int im, int kc, float4& ga, float4& gb) {
-      const int kq = kc * (kBK / 8) + lc;
-      if (kq < kq_max) {
-        const float4* gp = reinterpret_cast<const float4*>(p.gate + (size_t)im * p.cin) + 2 * kq;
-        ga = __ldg(gp);
-        gb = __ldg(gp + 1);
-      }
-    };
-    float4 g0n = make_float4(0.f, 0.f, 0.f, 0.f), g1n = g0n;
-    if (t_begin < t_end) fetch_gate(ti.img, 0, g0n, g1n);
-    for (int t = t_begin; t < t_end; t += t_step) {
-      const int img = ti.img;
+    for (int t = t_begin; t < t_end; t += t_step, ti.next()) {
       const int lrow0 = ti.sub * kBM;
       const int nrows = p.scale_b ? p.bn : min(kBM, p.rpi - lrow0);  // rows of the tile to scale
-      ti.next();  // ti now describes the NEXT tile (gate prefetch)
       for (int kc = 0; kc < p.k_chunks; ++kc) {
         const bool k_ok = kc * (kBK / 8) + lc < kq_max;
-        const float4 g0 = g0n, g1 = g1n;
-        if (kc + 1 < p.k_chunks) fetch_gate(img, kc + 1, g0n, g1n);
-        else if (t + t_step < t_end) fetch_gate(ti.img, 0, g0n, g1n);
-        mbar_wait(&full_bar[s], ph);
+        PROF_WAIT(0, mbar_wait(&full_bar[s], ph))
+        PROF_BEGIN
         if (k_ok) {
+          const float4* sg = reinterpret_cast<const float4*>(sgate + s * kBK) + 2 * lc;
+          const float4 g0 = sg[0], g1 = sg[1];
           uint8_t* base = smem + (size_t)s * stage_bytes + (p.scale_b ? kABytes : 0) + rg * 128 + (pc << 4);
           // source: the tile itself (scaled in place) or the resident pristine weights
           const uint8_t* src = p.b_res ? bres + (size_t)kc * b_bytes + rg * 128 + (pc << 4) : base;
@@ -402,12 +454,17 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               }
             }
           }
+          PROF_LAP(2)
           fence_proxy_async_smem();
+          PROF_LAP(3)
         }
-        mbar_arrive(&scaled_bar[s]);
+        __syncwarp();  // every lane's writes + proxy fence precede the warp's single arrival
+        if (lane == 0) mbar_arrive(&scaled_bar[s]);
+        PROF_LAP(4)
         if (++s == p.stages) { s = 0; ph ^= 1; }
       }
     }
+    if (ts < 32) { PROF_END(3) }
   }
 
   tcgen05_fence_before();
@@ -462,7 +519,8 @@ int encode_tmap_act_bf16(void* tmap_out, const void* base, long long m, int cols
 
 static size_t tc_smem_bytes(int bn, int stages, size_t bres_bytes) {
   return 1024 /*align slack*/ + (size_t)stages * (kABytes + bn * kBK * 2) + bres_bytes +
-         2 * kEpiWarps * kEpiStageBytes + kMaxBiasFloats * sizeof(float) + (3 * kMaxStages + 5) * sizeof(uint64_t) + 16;
+         2 * kEpiWarps * kEpiStageBytes + (kMaxBiasFloats + kMaxStages * kBK) * sizeof(float) +
+         (3 * kMaxStages + 5) * sizeof(uint64_t) + 16;
 }
 
 cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
@@ -470,6 +528,7 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   if (a.m >= (1ll << 31) - kBM || a.bn % 16 || a.bn < 16 || a.bn > 256 || a.cout_pad % a.bn || a.cin % 8 ||
       a.cout % 8 || a.cout_pad > kMaxBiasFloats || (a.cout_pad != a.bn && a.bn % 64))
     return cudaErrorInvalidValue;
+  if (a.gate && (reinterpret_cast<uintptr_t>(a.gate) & 15)) return cudaErrorInvalidValue;  // bulk-copied in 16-B units
   TcParams p;
   p.m = (int)a.m;
   p.cin = a.cin;
@@ -504,7 +563,23 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   int stages = kMaxStages;
   while (stages > 2 && tc_smem_bytes(a.bn, stages, bres_bytes) > budget) --stages;
   if (p.b_res && p.k_chunks <= stages) stages = stages / p.k_chunks * p.k_chunks;  // slot <-> K chunk mapping fixed
+  // producer lanes: every ring slot must belong to one producer (stages % np == 0)
+  static int np_max = -1;
+  if (np_max < 0) {
+    const char* e = getenv("B200DF_TC_NP");
+    np_max = e ? atoi(e) : 3;
+    if (np_max < 1 || np_max > 3) np_max = 3;
+  }
+  if (np_max >= 2 && !p.b_res && stages >= 5 && stages % 2 && stages % 3) --stages;  // 5 -> 4, 7 -> 6
+  p.np = (np_max >= 3 && stages % 3 == 0) ? 3 : ((np_max >= 2 && stages % 2 == 0) ? 2 : 1);
   p.stages = stages;
+#ifdef TC_PROF
+  static int prof_launch = 0;
+  p.prof_slot = prof_launch++ % kProfLaunches;
+  if (getenv("B200DF_TC_PROF_PRINT"))
+    fprintf(stderr, "tc_prof slot %d: m=%lld cin=%d cout=%d bn=%d stages=%d np=%d gate=%d scale_b=%d b_res=%d b_once=%d\n",
+            p.prof_slot, (long long)a.m, a.cin, a.cout, a.bn, stages, p.np, a.gate != nullptr, p.scale_b, p.b_res, p.b_once);
+#endif
   p.bias = a.bias;
   p.gate = a.gate;
   p.residual = reinterpret_cast<const bf16*>(a.residual);
@@ -542,3 +617,10 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
 }
 
 }  // namespace b200df
+
+#ifdef TC_PROF
+// dev builds only (not part of include/b200df.h): copies the role-timing table to the host
+extern "C" __attribute__((visibility("default"))) int b200df_tc_prof_read(unsigned long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, b200df::g_tc_prof, sizeof(b200df::g_tc_prof));
+}
+#endif
