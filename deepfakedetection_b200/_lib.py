@@ -14,7 +14,8 @@ from pathlib import Path
 
 _PKG = Path(__file__).resolve().parent
 REPO_ROOT = _PKG.parent
-LIB_PATH = _PKG / "libb200df.so"
+# B200DF_LIB: another build of the SAME library (A/B timing runs, the `make prof` build); never a fallback
+LIB_PATH = Path(os.environ["B200DF_LIB"]).resolve() if os.environ.get("B200DF_LIB") else _PKG / "libb200df.so"
 
 OK = 0
 E_INVALID, E_STATE, E_CUDA, E_NO_DEVICE, E_WORKSPACE = -1, -2, -3, -4, -5

@@ -18,6 +18,13 @@ typedef __nv_bfloat16 bf16;
 // ---- activations --------------------------------------------------------------------------
 // Accurate forms (fp32 strict path) and fast forms (bf16 path: one MUFU.TANH per element).
 __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
+// Programmatic dependent launch (kernels.h: launch_pdl): block until every prerequisite grid has completed and
+// its writes are visible; then let the next grid in the stream start placing its CTAs.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 __device__ __forceinline__ float silu_acc(float x) { return x / (1.0f + expf(-x)); }
 
 __device__ __forceinline__ float tanh_fast(float x) {

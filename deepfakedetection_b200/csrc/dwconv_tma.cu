@@ -140,7 +140,6 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
   };
 
   DwTile cur = decode((int)blockIdx.x);
-  if (tid == 0 && (int)blockIdx.x < total) issue(cur, 0);
 
   const int col_pairs = p.otw >> 1;
   const int per_img = col_pairs * (p.oth / TH);
@@ -166,6 +165,9 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
     bias2 = mul2(pack2(bb.x, bb.y), half2);
   };
   load_weights();
+  griddep_wait();  // weights, barriers and pool slots are ready; activations may only be touched from here on
+  griddep_launch_dependents();
+  if (tid == 0 && (int)blockIdx.x < total) issue(cur, 0);
 
   int it = 0;
   for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
@@ -323,9 +325,8 @@ cudaError_t dw_tma_launch(const DwPlan& pl, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
-  kern<<<pl.grid, pl.block, pl.smem, s>>>(*reinterpret_cast<const CUtensorMap*>(pl.tmap), pl.p);
   count_launch();
-  return cudaGetLastError();
+  return launch_pdl(kern, dim3(pl.grid), dim3(pl.block), pl.smem, s, *reinterpret_cast<const CUtensorMap*>(pl.tmap), pl.p);
 }
 
 template <int K, int S, int TH>

@@ -18,6 +18,14 @@ static thread_local long long g_launches = 0;
 
 namespace b200df {
 void count_launch(int n) { g_launches += n; }
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("B200DF_PDL");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
 }  // namespace b200df
 
 static int fail(int code, const char* fmt, ...) {

@@ -12,6 +12,27 @@ inline size_t dtype_size(int dt) { return dt == kBF16 ? 2 : 4; }
 // thread-local launch counter (bench.py's gpu_launches)
 void count_launch(int n = 1);
 
+// Programmatic dependent launch (PDL): the hot-path kernels run `griddepcontrol.wait` before they touch any
+// activation and trigger `griddepcontrol.launch_dependents` right after it, so the NEXT kernel's CTAs are placed
+// as SMs free up and its prologue (barrier init, TMEM alloc, weight/bias staging, tensor-map prefetch) overlaps
+// this kernel's tail.  Only kernels that contain the wait are launched through launch_pdl.  B200DF_PDL=0 -> off.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // error plumbing: launchers return cudaError_t of the launch (cudaGetLastError()).
 cudaError_t launch_stem(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias,
                         void* out, int dtype, cudaStream_t s);

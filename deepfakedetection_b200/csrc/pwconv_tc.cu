@@ -194,6 +194,8 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_ptr, 0);
+  griddep_wait();               // everything above touched only weights / shared memory / TMEM
+  griddep_launch_dependents();
 
   if (warp == 0 || warp == 2 || warp == 3) {
     // ================= TMA producers (up to three warps, one lane each) =================
@@ -600,9 +602,8 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
       if (e != cudaSuccess) return e;                                                                          \
       attr_done = true;                                                                                        \
     }                                                                                                          \
-    pwconv_tc_kernel<G_, A_, R_><<<grid, threads, smem, s>>>(*ta, *tb, *to, p);                                \
     count_launch();                                                                                            \
-    return cudaGetLastError();                                                                                 \
+    return launch_pdl(pwconv_tc_kernel<G_, A_, R_>, dim3(grid), dim3(threads), smem, s, *ta, *tb, *to, p);     \
   }
   TC_LAUNCH(false, 1, false)  // expand
   TC_LAUNCH(false, 0, false)  // conv_head

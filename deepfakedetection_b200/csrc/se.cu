@@ -25,6 +25,8 @@ se_kernel(const pool_t* __restrict__ pool, int n, int C, int RD, float inv_hw, c
   const int n0 = blockIdx.x * kSeG;
   const int ng = min(kSeG, n - n0);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  griddep_wait();
+  griddep_launch_dependents();
   for (int i = tid; i < kSeG * C; i += kSeThreads) {
     const int g = i / C, c = i - g * C;
     mean[i] = g < ng ? pool_value(pool[(size_t)(n0 + g) * C + c]) * inv_hw : 0.f;
@@ -78,9 +80,9 @@ cudaError_t launch_se(const pool_t* pool, int n, int c, int rd, float inv_hw, co
   if (c % 4) return cudaErrorInvalidValue;
   const size_t smem = (size_t)kSeG * (c + rd) * sizeof(float);
   if (smem > 48 * 1024) return cudaErrorInvalidValue;
-  se_kernel<<<(n + kSeG - 1) / kSeG, kSeThreads, smem, s>>>(pool, n, c, rd, inv_hw, w1, b1, w2t, b2, gate);
   count_launch();
-  return cudaGetLastError();
+  return launch_pdl(se_kernel, dim3((n + kSeG - 1) / kSeG), dim3(kSeThreads), smem, s, pool, n, c, rd, inv_hw, w1, b1,
+                    w2t, b2, gate);
 }
 
 }  // namespace b200df

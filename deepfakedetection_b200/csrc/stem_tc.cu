@@ -68,6 +68,8 @@ stem_tc_kernel(const void* __restrict__ xin, int n, int H, int W, const float* _
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  griddep_wait();  // `out` may still be read by the previous forward's kernels
+  griddep_launch_dependents();
   const uint32_t idesc = make_idesc_bf16_m128(32u);
   const uint64_t da = make_sw128_kmajor_desc(smem_u32(sA));
   const uint64_t db = make_sw128_kmajor_desc(smem_u32(sB));
@@ -170,10 +172,9 @@ static cudaError_t stem_tc_launch(const void* x, int n, int h, int w, const floa
   const long long tiles = (npix + kStT - 1) / kStT;
   const size_t smem = 1024 + kStT * 128 + 32 * 128 + 32 * sizeof(float) + 32;
   const int grid = (int)(tiles < (long long)kNumSMs * kStCtasPerSm ? tiles : (long long)kNumSMs * kStCtasPerSm);
-  stem_tc_kernel<kU8><<<grid, kStT, smem, s>>>(x, n, h, w, wgt, bias, reinterpret_cast<bf16*>(out), sc0, sc1, sc2, sh0,
-                                               sh1, sh2);
   count_launch();
-  return cudaGetLastError();
+  return launch_pdl(stem_tc_kernel<kU8>, dim3(grid), dim3(kStT), smem, s, x, n, h, w, wgt, bias,
+                    reinterpret_cast<bf16*>(out), sc0, sc1, sc2, sh0, sh1, sh2);
 }
 
 cudaError_t launch_stem_tc(const float* x, int n, int h, int w, const float* wgt, const float* bias, void* out,

@@ -15,39 +15,60 @@ namespace b200df {
 constexpr int kTailThreads = 256;
 
 // ---- head pool ----------------------------------------------------------------------------------
+// One CTA per image.  A thread owns (8-channel group, pixel phase q of Q): its pixels q, q+Q, ... are independent
+// 16-byte loads (all in flight at once), the Q partial sums meet in shared memory and are added in fixed order
+// (bit-reproducible).  Q is chosen so that ~1024 threads are busy whatever C is.
 template <typename T>
-__global__ void __launch_bounds__(kTailThreads)
-head_pool_kernel(const T* __restrict__ a, int HW, int C, const float* __restrict__ scale,
+__global__ void __launch_bounds__(1024)
+head_pool_kernel(const T* __restrict__ a, int HW, int C, int Q, const float* __restrict__ scale,
                  const float* __restrict__ shift, float* __restrict__ pooled) {
+  extern __shared__ float part[];  // [Q][C]
   const int n = blockIdx.x;
   const int CG = C >> 3;
   const float inv = 1.0f / (float)HW;
   const T* an = a + (size_t)n * HW * C;
-  for (int cg = threadIdx.x; cg < CG; cg += kTailThreads) {
+  for (int idx = threadIdx.x; idx < CG * Q; idx += blockDim.x) {
+    const int q = idx / CG, cg = idx - q * CG;
     float sc[8], sh[8], acc[8];
     load8<float>(scale + cg * 8, sc);
     load8<float>(shift + cg * 8, sh);
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-    for (int p = 0; p < HW; ++p) {
+    const T* ap = an + cg * 8;
+#pragma unroll 4
+    for (int p = q; p < HW; p += Q) {
       float v[8];
-      load8<T>(an + (size_t)p * C + cg * 8, v);
+      load8<T>(ap + (size_t)p * C, v);
 #pragma unroll
       for (int e = 0; e < 8; ++e) acc[e] += silu_acc(fmaf(v[e], sc[e], sh[e]));
     }
-#pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] *= inv;
-    store8<float>(pooled + (size_t)n * C + cg * 8, acc);
+    store8<float>(part + (size_t)q * C + cg * 8, acc);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float v = 0.f;
+    for (int q = 0; q < Q; ++q) v += part[(size_t)q * C + c];
+    pooled[(size_t)n * C + c] = v * inv;
   }
 }
 
 cudaError_t launch_head_pool(const void* a, int n, int hw, int c, const float* scale, const float* shift,
                              float* pooled, int dtype, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
+  const int cg = c >> 3;
+  if (cg < 1) return cudaErrorInvalidValue;
+  int q = 1024 / cg;
+  q = q < 1 ? 1 : (q > 8 ? 8 : q);
+  if (q > hw) q = hw > 0 ? hw : 1;
+  while (q > 1 && (size_t)q * c * sizeof(float) > 48 * 1024) --q;
+  if ((size_t)q * c * sizeof(float) > 48 * 1024) return cudaErrorInvalidValue;
+  int threads = (cg * q + 31) / 32 * 32;
+  if (threads > 1024) threads = 1024;
+  const size_t smem = (size_t)q * c * sizeof(float);
   if (dtype == kBF16)
-    head_pool_kernel<bf16><<<n, kTailThreads, 0, s>>>(reinterpret_cast<const bf16*>(a), hw, c, scale, shift, pooled);
+    head_pool_kernel<bf16><<<n, threads, smem, s>>>(reinterpret_cast<const bf16*>(a), hw, c, q, scale, shift, pooled);
   else
-    head_pool_kernel<float><<<n, kTailThreads, 0, s>>>(reinterpret_cast<const float*>(a), hw, c, scale, shift, pooled);
+    head_pool_kernel<float><<<n, threads, smem, s>>>(reinterpret_cast<const float*>(a), hw, c, q, scale, shift, pooled);
   count_launch();
   return cudaGetLastError();
 }
