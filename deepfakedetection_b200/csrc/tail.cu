@@ -27,6 +27,8 @@ head_pool_kernel(const T* __restrict__ a, int HW, int C, int Q, const float* __r
   const int CG = C >> 3;
   const float inv = 1.0f / (float)HW;
   const T* an = a + (size_t)n * HW * C;
+  griddep_wait();
+  griddep_launch_dependents();
   for (int idx = threadIdx.x; idx < CG * Q; idx += blockDim.x) {
     const int q = idx / CG, cg = idx - q * CG;
     float sc[8], sh[8], acc[8];
@@ -65,12 +67,12 @@ cudaError_t launch_head_pool(const void* a, int n, int hw, int c, const float* s
   int threads = (cg * q + 31) / 32 * 32;
   if (threads > 1024) threads = 1024;
   const size_t smem = (size_t)q * c * sizeof(float);
-  if (dtype == kBF16)
-    head_pool_kernel<bf16><<<n, threads, smem, s>>>(reinterpret_cast<const bf16*>(a), hw, c, q, scale, shift, pooled);
-  else
-    head_pool_kernel<float><<<n, threads, smem, s>>>(reinterpret_cast<const float*>(a), hw, c, q, scale, shift, pooled);
   count_launch();
-  return cudaGetLastError();
+  if (dtype == kBF16)
+    return launch_pdl(head_pool_kernel<bf16>, dim3(n), dim3(threads), smem, s, reinterpret_cast<const bf16*>(a), hw, c, q,
+                      scale, shift, pooled);
+  return launch_pdl(head_pool_kernel<float>, dim3(n), dim3(threads), smem, s, reinterpret_cast<const float*>(a), hw, c, q,
+                    scale, shift, pooled);
 }
 
 // ---- classifier ---------------------------------------------------------------------------------
@@ -79,6 +81,8 @@ classifier_kernel(const float* __restrict__ pooled, int C, const float* __restri
                   int NC, float* __restrict__ logits) {
   const int n = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const float* pn = pooled + (size_t)n * C;
+  griddep_wait();
+  griddep_launch_dependents();
   for (int j = warp; j < NC; j += 4) {
     float s = 0.f;
     for (int c = lane; c < C; c += 32) s = fmaf(__ldg(w + (size_t)j * C + c), pn[c], s);
@@ -90,19 +94,18 @@ classifier_kernel(const float* __restrict__ pooled, int C, const float* __restri
 cudaError_t launch_classifier(const float* pooled, int n, int c, const float* w, const float* b, int num_classes,
                               float* logits, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
-  classifier_kernel<<<n, 128, 0, s>>>(pooled, c, w, b, num_classes, logits);
   count_launch();
-  return cudaGetLastError();
+  return launch_pdl(classifier_kernel, dim3(n), dim3(128), 0, s, pooled, c, w, b, num_classes, logits);
 }
 
 // ---- fused Grad-CAM -------------------------------------------------------------------------------
 // w[n,k] = Wfc[c_n,k]/HW * scale_k * mean_hw silu'(A*scale_k + shift_k);  cam[n,p] = relu(sum_k w[n,k] A[n,p,k])
 template <typename T>
-__global__ void __launch_bounds__(kTailThreads)
-cam_kernel(const T* __restrict__ a, int HW, int C, const float* __restrict__ scale, const float* __restrict__ shift,
+__global__ void __launch_bounds__(1024)
+cam_kernel(const T* __restrict__ a, int HW, int C, int Q, const float* __restrict__ scale, const float* __restrict__ shift,
            const float* __restrict__ wfc, int NC, const int32_t* __restrict__ target, const float* __restrict__ logits,
            float* __restrict__ cam) {
-  extern __shared__ float wk[];  // [C]
+  extern __shared__ float wk[];  // [C] weights + [Q][C] partial sums
   const int n = blockIdx.x;
   const int CG = C >> 3;
   const T* an = a + (size_t)n * HW * C;
@@ -119,14 +122,18 @@ cam_kernel(const T* __restrict__ a, int HW, int C, const float* __restrict__ sca
   }
   cls = min(max(cls, 0), NC - 1);
   const float inv = 1.0f / (float)HW;
-  for (int cg = threadIdx.x; cg < CG; cg += kTailThreads) {
-    float sc[8], sh[8], acc[8], wf[8];
+  // mean_hw silu'(.) per channel: (8-channel group, pixel phase q of Q) per thread, Q partial sums combined in
+  // fixed order (same scheme as head_pool_kernel)
+  float* part = wk + C;  // [Q][C]
+  for (int idx = threadIdx.x; idx < CG * Q; idx += blockDim.x) {
+    const int q = idx / CG, cg = idx - q * CG;
+    float sc[8], sh[8], acc[8];
     load8<float>(scale + cg * 8, sc);
     load8<float>(shift + cg * 8, sh);
-    load8<float>(wfc + (size_t)cls * C + cg * 8, wf);
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-    for (int p = 0; p < HW; ++p) {
+#pragma unroll 4
+    for (int p = q; p < HW; p += Q) {
       float v[8];
       load8<T>(an + (size_t)p * C + cg * 8, v);
 #pragma unroll
@@ -136,12 +143,17 @@ cam_kernel(const T* __restrict__ a, int HW, int C, const float* __restrict__ sca
         acc[e] += sg * fmaf(z, 1.0f - sg, 1.0f);  // silu'(z)
       }
     }
-#pragma unroll
-    for (int e = 0; e < 8; ++e) wk[cg * 8 + e] = wf[e] * inv * sc[e] * (acc[e] * inv);
+    store8<float>(part + (size_t)q * C + cg * 8, acc);
   }
   __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int p = warp; p < HW; p += kTailThreads / 32) {
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f;
+    for (int q = 0; q < Q; ++q) a += part[(size_t)q * C + c];
+    wk[c] = __ldg(wfc + (size_t)cls * C + c) * inv * __ldg(scale + c) * (a * inv);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int p = warp; p < HW; p += nw) {
     float s = 0.f;
     for (int cg = lane; cg < CG; cg += 32) {
       float v[8];
@@ -159,13 +171,22 @@ cudaError_t launch_cam(const void* a, int n, int hw, int c, const float* scale, 
                        cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   if (target_cls == nullptr && logits == nullptr) return cudaErrorInvalidValue;
+  const int cg = c >> 3;
+  if (cg < 1) return cudaErrorInvalidValue;
+  int q = 1024 / cg;
+  q = q < 1 ? 1 : (q > 8 ? 8 : q);
+  if (q > hw) q = hw > 0 ? hw : 1;
+  while (q > 1 && (size_t)(q + 1) * c * sizeof(float) > 48 * 1024) --q;
+  const size_t smem = (size_t)(q + 1) * c * sizeof(float);
+  if (smem > 48 * 1024) return cudaErrorInvalidValue;
+  int threads = (cg * q + 31) / 32 * 32;
+  threads = threads > 1024 ? 1024 : (threads < 256 ? 256 : threads);
   if (dtype == kBF16)
-    cam_kernel<bf16><<<n, kTailThreads, c * sizeof(float), s>>>(reinterpret_cast<const bf16*>(a), hw, c, scale, shift,
-                                                                 wfc, num_classes, target_cls, logits, cam_lowres);
+    cam_kernel<bf16><<<n, threads, smem, s>>>(reinterpret_cast<const bf16*>(a), hw, c, q, scale, shift, wfc, num_classes,
+                                              target_cls, logits, cam_lowres);
   else
-    cam_kernel<float><<<n, kTailThreads, c * sizeof(float), s>>>(reinterpret_cast<const float*>(a), hw, c, scale,
-                                                                  shift, wfc, num_classes, target_cls, logits,
-                                                                  cam_lowres);
+    cam_kernel<float><<<n, threads, smem, s>>>(reinterpret_cast<const float*>(a), hw, c, q, scale, shift, wfc,
+                                               num_classes, target_cls, logits, cam_lowres);
   count_launch();
   return cudaGetLastError();
 }
@@ -203,50 +224,78 @@ __device__ __forceinline__ float bilerp(const float* src, int side, int oy, int 
   return top + (bot - top) * fy;
 }
 
-__global__ void __launch_bounds__(kTailThreads)
+// One CTA (1024 threads) per image.  The bilinear sample positions are separable: per-axis (i0, i1, frac) tables
+// in shared memory, a warp per output row, lanes along the row (coalesced stores, no divisions).  Same arithmetic
+// as bilerp() above, evaluated twice per pixel (min/max pass, write pass) instead of three times.
+constexpr int kUpThreads = 1024;
+__global__ void __launch_bounds__(kUpThreads)
 cam_upsample_kernel(const float* __restrict__ cam_low, int side, int out_side, float* __restrict__ cam) {
-  extern __shared__ float sm[];  // [side*side] + reduction scratch
+  extern __shared__ float sm[];  // [side*side] + 64 reduction scratch + 3 tables of out_side
   float* src = sm;
   float* red = sm + side * side;
-  const int n = blockIdx.x, tid = threadIdx.x;
+  int* t0 = reinterpret_cast<int*>(red + 64);
+  int* t1 = t0 + out_side;
+  float* tf = reinterpret_cast<float*>(t1 + out_side);
+  const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = kUpThreads / 32;
   const int S2 = side * side;
+  auto reduce2 = [&](float& lo, float& hi) {  // block-wide min and max
+    lo = warp_min(lo);
+    hi = warp_max(hi);
+    __syncthreads();
+    if (lane == 0) { red[warp] = lo; red[32 + warp] = hi; }
+    __syncthreads();
+    lo = red[0]; hi = red[32];
+    for (int i = 1; i < nw; ++i) { lo = fminf(lo, red[i]); hi = fmaxf(hi, red[32 + i]); }
+  };
   float lo = INFINITY, hi = -INFINITY;
-  for (int i = tid; i < S2; i += kTailThreads) {
-    float v = cam_low[(size_t)n * S2 + i];
+  for (int i = tid; i < S2; i += kUpThreads) {
+    const float v = cam_low[(size_t)n * S2 + i];
     src[i] = v;
     lo = fminf(lo, v);
+    hi = fmaxf(hi, v);
   }
-  lo = block_reduce_min(lo, red);
-  for (int i = tid; i < S2; i += kTailThreads) hi = fmaxf(hi, src[i] - lo);
-  hi = block_reduce_max(hi, red);
-  const float inv = 1.0f / (hi + 1e-7f);
-  for (int i = tid; i < S2; i += kTailThreads) src[i] = (src[i] - lo) * inv;
-  __syncthreads();
   const float rscale = (float)side / (float)out_side;
-  const int O2 = out_side * out_side;
+  for (int o = tid; o < out_side; o += kUpThreads) {
+    const float sp = fmaxf(((float)o + 0.5f) * rscale - 0.5f, 0.f);
+    const int i0 = min((int)sp, side - 1);
+    t0[o] = i0;
+    t1[o] = min(i0 + 1, side - 1);
+    tf[o] = sp - (float)i0;
+  }
+  reduce2(lo, hi);
+  hi = hi - lo;  // == max over (v - lo): rounding is monotonic
+  const float inv = 1.0f / (hi + 1e-7f);
+  __syncthreads();
+  for (int i = tid; i < S2; i += kUpThreads) src[i] = (src[i] - lo) * inv;
+  __syncthreads();
+  auto sample = [&](int oy, int ox) {
+    const int y0 = t0[oy], y1 = t1[oy], x0 = t0[ox], x1 = t1[ox];
+    const float fy = tf[oy], fx = tf[ox];
+    const float v00 = src[y0 * side + x0], v01 = src[y0 * side + x1];
+    const float v10 = src[y1 * side + x0], v11 = src[y1 * side + x1];
+    const float top = v00 + (v01 - v00) * fx, bot = v10 + (v11 - v10) * fx;
+    return fmaxf(top + (bot - top) * fy, 0.f);
+  };
   float lo2 = INFINITY, hi2 = -INFINITY;
-  for (int i = tid; i < O2; i += kTailThreads) {
-    float v = fmaxf(bilerp(src, side, i / out_side, i % out_side, rscale), 0.f);
-    lo2 = fminf(lo2, v);
-  }
-  lo2 = block_reduce_min(lo2, red);
-  for (int i = tid; i < O2; i += kTailThreads) {
-    float v = fmaxf(bilerp(src, side, i / out_side, i % out_side, rscale), 0.f);
-    hi2 = fmaxf(hi2, v - lo2);
-  }
-  hi2 = block_reduce_max(hi2, red);
+  for (int oy = warp; oy < out_side; oy += nw)
+    for (int ox = lane; ox < out_side; ox += 32) {
+      const float v = sample(oy, ox);
+      lo2 = fminf(lo2, v);
+      hi2 = fmaxf(hi2, v);
+    }
+  reduce2(lo2, hi2);
+  hi2 = hi2 - lo2;
   const float inv2 = 1.0f / (hi2 + 1e-7f);
-  float* on = cam + (size_t)n * O2;
-  for (int i = tid; i < O2; i += kTailThreads) {
-    float v = fmaxf(bilerp(src, side, i / out_side, i % out_side, rscale), 0.f);
-    on[i] = (v - lo2) * inv2;
-  }
+  float* on = cam + (size_t)n * out_side * out_side;
+  for (int oy = warp; oy < out_side; oy += nw)
+    for (int ox = lane; ox < out_side; ox += 32) on[oy * out_side + ox] = (sample(oy, ox) - lo2) * inv2;
 }
 
 cudaError_t launch_cam_upsample(const float* cam_lowres, int n, int side, int out_side, float* cam, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
-  size_t smem = (side * side + 32) * sizeof(float);
-  cam_upsample_kernel<<<n, kTailThreads, smem, s>>>(cam_lowres, side, out_side, cam);
+  const size_t smem = (size_t)(side * side + 64 + 3 * out_side) * sizeof(float);
+  if (smem > 48 * 1024) return cudaErrorInvalidValue;
+  cam_upsample_kernel<<<n, kUpThreads, smem, s>>>(cam_lowres, side, out_side, cam);
   count_launch();
   return cudaGetLastError();
 }
@@ -342,6 +391,8 @@ cudaError_t launch_head_backward(const float* a, const float* grad_logits, int n
 __global__ void softmax_pack_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, int n,
                                     int NC, float* __restrict__ packed) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  griddep_wait();
+  griddep_launch_dependents();
   if (i >= n) return;
   const float* l = logits + (size_t)i * NC;
   float mx = l[0];
@@ -359,9 +410,8 @@ __global__ void softmax_pack_kernel(const float* __restrict__ logits, const int6
 cudaError_t launch_softmax_pack(const float* logits, const int64_t* labels, int n, int num_classes, float* packed,
                                 cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
-  softmax_pack_kernel<<<(n + 127) / 128, 128, 0, s>>>(logits, labels, n, num_classes, packed);
   count_launch();
-  return cudaGetLastError();
+  return launch_pdl(softmax_pack_kernel, dim3((n + 127) / 128), dim3(128), 0, s, logits, labels, n, num_classes, packed);
 }
 
 }  // namespace b200df

@@ -29,3 +29,14 @@ with torch.inference_mode():
     t2 = time.perf_counter()
 print(f"n={n}: device {e0.elapsed_time(e1) / K:.4f} ms/step, host enqueue {(t1 - t0) / K * 1e3:.4f} ms/step, "
       f"wall {(t2 - t0) / K * 1e3:.4f} ms/step")
+if len(sys.argv) > 2 and sys.argv[2] == "prof":
+    import cProfile
+    import pstats
+    pr = cProfile.Profile()
+    with torch.inference_mode():
+        pr.enable()
+        for _ in range(K):
+            m(x)
+        pr.disable()
+        torch.cuda.synchronize()
+    pstats.Stats(pr).sort_stats("tottime").print_stats(12)
