@@ -24,6 +24,7 @@
 #include "kernels.h"
 #include "tc.cuh"
 
+#include <stdio.h>
 #include <stdlib.h>
 
 #include <algorithm>
@@ -68,8 +69,8 @@ __device__ __forceinline__ f32x2 bf16x2_to_f32x2(uint32_t raw) {
 
 struct DwTile { int cb, tx, ty, ng; };
 
-template <int K, int S, int TH>
-__global__ void __launch_bounds__(256)
+template <int K, int S, int TH, int NC>
+__global__ void __launch_bounds__(256, 2)
 dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-align by OFFSET (not by pointer round-trip) so the compiler keeps the shared address space -> LDS
@@ -141,7 +142,11 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
 
   DwTile cur = decode((int)blockIdx.x);
 
-  const int col_pairs = p.otw >> 1;
+  // a warp covers 2*NC output columns: half-warp xs takes columns x and (NC == 2) x + 2, so that the two
+  // half-warps still read adjacent 64-B pixels (bank-conflict free) while a thread's two columns share K - 2
+  // of the K + 2 inputs it loads per row
+  constexpr int KV = K + 2 * (NC - 1);
+  const int col_pairs = p.otw / (2 * NC);
   const int per_img = col_pairs * (p.oth / TH);
   const int items = per_img * p.gimg;
   const int row_bytes = (S == 1) ? p.bw * 64 : p.bw * 128;  // S=2: two parity planes of bw pairs per row
@@ -186,21 +191,25 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
 
     for (int item = warp; item < items; item += nwarps) {
       const int g = (item * p.inv_per_img) >> 16;           // image inside the group
+      if (cur.ng * p.gimg + g >= p.n) continue;             // ragged last group (the plan never depends on n,
+                                                            // so a sample's result never depends on its batch)
       const int rem = item - g * per_img;
       const int st = (rem * p.inv_cp) >> 16;                // row strip
-      const int x = (rem - st * col_pairs) * 2 + xs;        // output column inside the tile
+      const int x = (rem - st * col_pairs) * (2 * NC) + xs; // first output column inside the tile
       const int y0 = st * TH;                               // first output row inside the tile
-      f32x2 acc[TH];
+      f32x2 acc[NC][TH];
 #pragma unroll
-      for (int j = 0; j < TH; ++j) acc[j] = bias2;
+      for (int q = 0; q < NC; ++q)
+#pragma unroll
+        for (int j = 0; j < TH; ++j) acc[q][j] = bias2;
 
       // (input row 0 of the strip, this thread's first column, its channel pair)
       const uint8_t* base = tile + (g * p.img_bytes + y0 * S * row_bytes + x * 64 + cp * 4);
 #pragma unroll
       for (int rr = 0; rr < RIN; ++rr) {
-        f32x2 v[K];
+        f32x2 v[KV];
 #pragma unroll
-        for (int kx = 0; kx < K; ++kx) {
+        for (int kx = 0; kx < KV; ++kx) {
           uint32_t raw;
           if constexpr (S == 1) {
             raw = *reinterpret_cast<const uint32_t*>(base + rr * row_bytes + kx * 64);
@@ -216,30 +225,35 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
           if ((rr - ky) >= 0 && (rr - ky) % S == 0 && (rr - ky) / S < TH) {
             const int j = (rr - ky) / S;
 #pragma unroll
-            for (int kx = 0; kx < K; ++kx) acc[j] = fma2(v[kx], w[ky * K + kx], acc[j]);
+            for (int q = 0; q < NC; ++q)
+#pragma unroll
+              for (int kx = 0; kx < K; ++kx) acc[q][j] = fma2(v[kx + 2 * q], w[ky * K + kx], acc[q][j]);
           }
         }
       }
       // epilogue: SiLU (h + h*tanh h), bf16 pack, store, pool partials
-      const int ox = cur.tx * p.otw + x;
       const int oy0 = cur.ty * p.oth + y0;
       const int img = cur.ng * p.gimg + g;
       f32x2 ps = 0ull;
-      if (c_ok && ox < p.Wo && img < p.n) {
-        bf16* op = reinterpret_cast<bf16*>(p.out) + (((size_t)img * p.Ho + oy0) * p.Wo + ox) * p.C + c0;
-        const bool rows_full = oy0 + TH <= p.Ho;
 #pragma unroll
-        for (int j = 0; j < TH; ++j) {
-          float h0, h1;
-          unpack2(acc[j], h0, h1);
-          const f32x2 f = fma2(acc[j], pack2(tanh_fast(h0), tanh_fast(h1)), acc[j]);
-          float f0, f1;
-          unpack2(f, f0, f1);
-          if (rows_full || oy0 + j < p.Ho) {
-            *reinterpret_cast<uint32_t*>(op) = pack_bf16x2(f0, f1);
-            ps = add2(ps, f);
+      for (int q = 0; q < NC; ++q) {
+        const int ox = cur.tx * p.otw + x + 2 * q;
+        if (c_ok && ox < p.Wo && img < p.n) {
+          bf16* op = reinterpret_cast<bf16*>(p.out) + (((size_t)img * p.Ho + oy0) * p.Wo + ox) * p.C + c0;
+          const bool rows_full = oy0 + TH <= p.Ho;
+#pragma unroll
+          for (int j = 0; j < TH; ++j) {
+            float h0, h1;
+            unpack2(acc[q][j], h0, h1);
+            const f32x2 f = fma2(acc[q][j], pack2(tanh_fast(h0), tanh_fast(h1)), acc[q][j]);
+            float f0, f1;
+            unpack2(f, f0, f1);
+            if (rows_full || oy0 + j < p.Ho) {
+              *reinterpret_cast<uint32_t*>(op) = pack_bf16x2(f0, f1);
+              ps = add2(ps, f);
+            }
+            op += out_row;
           }
-          op += out_row;
         }
       }
       if (p.pool != nullptr) {
@@ -316,9 +330,9 @@ int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsign
 
 namespace {
 
-template <int K, int S, int TH>
+template <int K, int S, int TH, int NC>
 cudaError_t dw_tma_launch(const DwPlan& pl, cudaStream_t s) {
-  auto kern = dwconv_tma_kernel<K, S, TH>;
+  auto kern = dwconv_tma_kernel<K, S, TH, NC>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -329,20 +343,21 @@ cudaError_t dw_tma_launch(const DwPlan& pl, cudaStream_t s) {
   return launch_pdl(kern, dim3(pl.grid), dim3(pl.block), pl.smem, s, *reinterpret_cast<const CUtensorMap*>(pl.tmap), pl.p);
 }
 
-template <int K, int S, int TH>
+template <int K, int S, int TH, int NC>
 int dw_tma_occupancy(int block, size_t smem) {
-  auto kern = dwconv_tma_kernel<K, S, TH>;
+  auto kern = dwconv_tma_kernel<K, S, TH, NC>;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) return 1;
   int nb = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, block, smem) != cudaSuccess || nb < 1) nb = 1;
   return nb;
 }
 
-int dw_tma_occupancy_dispatch(int k, int stride, int th, int block, size_t smem) {
-#define DW_OCC(K_, S_, TH_) \
-  if (k == K_ && stride == S_ && th == TH_) return dw_tma_occupancy<K_, S_, TH_>(block, smem)
-  DW_OCC(3, 1, 8); DW_OCC(3, 1, 7); DW_OCC(3, 2, 8); DW_OCC(3, 2, 7);
-  DW_OCC(5, 1, 8); DW_OCC(5, 1, 7); DW_OCC(5, 2, 8); DW_OCC(5, 2, 7);
+int dw_tma_occupancy_dispatch(int k, int stride, int th, int nc, int block, size_t smem) {
+#define DW_OCC(K_, S_, TH_, NC_) \
+  if (k == K_ && stride == S_ && th == TH_ && nc == NC_) return dw_tma_occupancy<K_, S_, TH_, NC_>(block, smem)
+  DW_OCC(3, 1, 8, 1); DW_OCC(3, 1, 7, 1); DW_OCC(3, 2, 8, 1); DW_OCC(3, 2, 7, 1);
+  DW_OCC(5, 1, 8, 1); DW_OCC(5, 1, 7, 1); DW_OCC(5, 2, 8, 1); DW_OCC(5, 2, 7, 1);
+  DW_OCC(3, 1, 8, 2); DW_OCC(3, 1, 7, 2); DW_OCC(5, 1, 7, 2);
 #undef DW_OCC
   return 1;
 }
@@ -369,39 +384,70 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
   if (stride == 2 && (w & 1)) return -1;
   const int pad = (k - 1) / 2;
   const int Ho = (h + 2 * pad - k) / stride + 1, Wo = (w + 2 * pad - k) / stride + 1;
-  const int th = (Ho % 8 == 0) ? 8 : 7;
-  const int strips_total = (Ho + th - 1) / th;
-  // choose the output tile: even width wasting at most one column, height a multiple of TH dividing the
-  // strip count; maximise useful/loaded pixels subject to the per-stage smem limit, prefer >= 8 warp items
-  double best_score = -1.0;
-  int b_otw = 0, b_m = 0, b_bw = 0, b_bh = 0, b_g = 1;
-  for (int otw = 2; otw <= 32; otw += 2) {
-    const int tiles_x = (Wo + otw - 1) / otw;
-    if (tiles_x * otw - Wo > 1) continue;
-    for (int m = 1; m <= strips_total; ++m) {
-      if (strips_total % m) continue;
-      const int oth = m * th;
-      int bw, bh = (oth - 1) * stride + k;
-      size_t bytes;
-      if (stride == 1) {
-        bw = otw + k - 1;
-        bytes = (size_t)bw * bh * 64;
-      } else {
-        const int cols = (otw - 1) * 2 + k + (2 - pad);  // incl. the even-start offset
-        bw = (cols + 1) / 2;                              // column pairs
-        bytes = (size_t)bw * 2 * bh * 64;
+  // choose the strip height TH and the output tile: even width wasting at most one column, height a multiple
+  // of TH dividing the strip count; maximise useful/loaded pixels subject to the per-stage smem limit, prefer
+  // >= 8 warp items.  A few EfficientNet-B0 shapes have measured-better plans (tools/dw_sweep.py on a B200);
+  // B200DF_DW_PLAN="th,otw,m,g" pins the choice for such sweeps.
+  int f_th = 0, f_otw = 0, f_m = 0, f_g = 0, nc = 1;
+  if (const char* e = getenv("B200DF_DW_PLAN")) {
+    const int got = sscanf(e, "%d,%d,%d,%d,%d", &f_th, &f_otw, &f_m, &f_g, &nc);
+    if (got < 4) f_th = f_otw = f_m = f_g = 0;
+    if (got < 5) nc = 1;
+  } else {
+    // measured on a B200 at N = 256 (tools/dw_sweep.py); nc = 2: two output columns per thread
+    struct Tuned { int h, k, stride, th, otw, m, g, nc; };
+    static const Tuned tuned[] = {
+        {112, 3, 1, 7, 16, 4, 1, 2},  // 3x3 s1 112^2, C=32  : 0.110 -> 0.100 ms
+        {112, 3, 2, 7, 14, 1, 1, 1},  // 3x3 s2 112->56, C=96: 0.130 -> 0.125 ms
+        {56, 3, 1, 7, 8, 8, 1, 2},    // 3x3 s1 56^2, C=144  : 0.139 -> 0.125 ms
+        {56, 5, 2, 7, 4, 4, 1, 1},    // 5x5 s2 56->28       : 0.094 -> 0.082 ms
+        {28, 5, 1, 7, 4, 4, 1, 2},    // 5x5 s1 28^2, C=240  : 0.106 -> 0.098 ms
+        {14, 5, 2, 7, 8, 1, 1, 1},    // 5x5 s2 14->7        : 0.031 -> 0.030 ms
+        {7, 5, 1, 7, 8, 1, 4, 2},     // 5x5 s1 7^2, C=1152  : 0.040 -> 0.035 ms
+        {7, 3, 1, 7, 8, 1, 4, 2},     // 3x3 s1 7^2, C=1152  : 0.026 -> 0.022 ms
+    };
+    for (const Tuned& t : tuned)
+      if (t.h == h && h == w && t.k == k && t.stride == stride) {
+        f_th = t.th; f_otw = t.otw; f_m = t.m; f_g = t.g; nc = t.nc;
       }
-      if (bw > 256 || bh > 256) continue;
-      const bool whole = tiles_x == 1 && m == strips_total;  // the tile is the whole image
-      for (int g = 1; g <= (whole ? kDwMaxGroup : 1); g *= 2) {
-        if (g > n && g > 1) break;
-        if (2 * ((bytes * g + 1023) & ~size_t(1023)) + 2 * 8 * (size_t)g * kDwCB * 4 + 1024 > kDwSmemLimit) break;
-        const int items = (otw / 2) * m * g;
-        double eff = (double)std::min(otw, Wo) * std::min(oth, Ho) * stride * stride / ((double)bytes / 64.0);
-        double score = eff * std::min(1.0, 0.5 + items / 32.0);
-        if (score > best_score) {
-          best_score = score;
-          b_otw = otw; b_m = m; b_bw = bw; b_bh = bh; b_g = g;
+  }
+  if (nc != 1 && (nc != 2 || stride != 1 || (k == 5 && f_th == 8))) return -1;
+  double best_score = -1.0;
+  int b_otw = 0, b_m = 0, b_bw = 0, b_bh = 0, b_g = 1, th = 8, strips_total = 0;
+  for (int th_c = 8; th_c >= 7; --th_c) {
+    if (f_th ? th_c != f_th : th_c != ((Ho % 8 == 0) ? 8 : 7)) continue;
+    const int strips_c = (Ho + th_c - 1) / th_c;
+    for (int otw = 2 * nc; otw <= 32; otw += 2 * nc) {
+      if (f_otw && otw != f_otw) continue;
+      const int tiles_x = (Wo + otw - 1) / otw;
+      if (!f_otw && tiles_x * otw - Wo > 1) continue;
+      for (int m = 1; m <= strips_c; ++m) {
+        if (strips_c % m) continue;
+        if (f_m && m != f_m) continue;
+        const int oth = m * th_c;
+        int bw, bh = (oth - 1) * stride + k;
+        size_t bytes;
+        if (stride == 1) {
+          bw = otw + k - 1;
+          bytes = (size_t)bw * bh * 64;
+        } else {
+          const int cols = (otw - 1) * 2 + k + (2 - pad);  // incl. the even-start offset
+          bw = (cols + 1) / 2;                              // column pairs
+          bytes = (size_t)bw * 2 * bh * 64;
+        }
+        if (bw > 256 || bh > 256) continue;
+        const bool whole = tiles_x == 1 && m == strips_c;  // the tile is the whole image
+        for (int g = 1; g <= (whole ? kDwMaxGroup : 1); g *= 2) {
+          if (f_g && g != f_g) continue;
+          if (2 * ((bytes * g + 1023) & ~size_t(1023)) + 2 * 8 * (size_t)g * kDwCB * 4 + 1024 > kDwSmemLimit) break;
+          const int items = (otw / (2 * nc)) * m * g;
+          double eff = (double)std::min(otw, Wo) * std::min(oth, Ho) * stride * stride / ((double)bytes / 64.0);
+          double score = eff * std::min(1.0, 0.5 + items / 32.0);
+          if (score > best_score) {
+            best_score = score;
+            b_otw = otw; b_m = m; b_bw = bw; b_bh = bh; b_g = g;
+            th = th_c; strips_total = strips_c;
+          }
         }
       }
     }
@@ -417,8 +463,9 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
   p.bw = b_bw; p.bh = b_bh;
   p.gimg = b_g;
   p.img_bytes = (int)((stride == 1 ? (size_t)b_bw : (size_t)b_bw * 2) * b_bh * 64);
-  p.inv_cp = (65536 + b_otw / 2 - 1) / (b_otw / 2);
-  p.inv_per_img = (65536 + (b_otw / 2) * b_m - 1) / ((b_otw / 2) * b_m);
+  const int col_groups = b_otw / (2 * nc);
+  p.inv_cp = (65536 + col_groups - 1) / col_groups;
+  p.inv_per_img = (65536 + col_groups * b_m - 1) / (col_groups * b_m);
   p.box_bytes = (uint32_t)p.img_bytes * (uint32_t)b_g;
   p.stage_stride = (int)((p.box_bytes + 1023) & ~1023u);
   p.wgt = wgt; p.bias = bias; p.out = out; p.pool = pool;
@@ -436,12 +483,12 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
     rc = encode_tmap_nd_bf16(plan.tmap, x, 5, dims, str, box, 0);
   }
   if (rc) return rc;
-  plan.k = k; plan.stride = stride; plan.th = th;
-  const int items = (b_otw / 2) * b_m * b_g;
+  plan.k = k; plan.stride = stride; plan.th = th; plan.nc = nc;
+  const int items = col_groups * b_m * b_g;
   plan.block = items >= 8 ? 256 : (items >= 4 ? 128 : 64);
   plan.smem = 1024 + 2 * (size_t)p.stage_stride + 2 * (size_t)(plan.block / 32) * b_g * kDwCB * sizeof(float);
   const long long total = (long long)p.tiles_x * p.tiles_y * p.ncb * ((n + b_g - 1) / b_g);
-  const int per_sm = dw_tma_occupancy_dispatch(k, stride, th, plan.block, plan.smem);
+  const int per_sm = dw_tma_occupancy_dispatch(k, stride, th, nc, plan.block, plan.smem);
   long long grid = std::min<long long>(total, (long long)kNumSMs * per_sm);
   p.cb_fixed = 0;
   if (grid >= p.ncb) {  // a grid that is a multiple of ncb keeps every CTA on one channel block
@@ -455,10 +502,11 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
 
 cudaError_t launch_dwconv_tma(const DwPlan& pl, cudaStream_t s) {
   if (pl.tc) return launch_dwconv_tc(pl, s);
-#define DW_CASE(K_, S_, TH_) \
-  if (pl.k == K_ && pl.stride == S_ && pl.th == TH_) return dw_tma_launch<K_, S_, TH_>(pl, s)
-  DW_CASE(3, 1, 8); DW_CASE(3, 1, 7); DW_CASE(3, 2, 8); DW_CASE(3, 2, 7);
-  DW_CASE(5, 1, 8); DW_CASE(5, 1, 7); DW_CASE(5, 2, 8); DW_CASE(5, 2, 7);
+#define DW_CASE(K_, S_, TH_, NC_) \
+  if (pl.k == K_ && pl.stride == S_ && pl.th == TH_ && pl.nc == NC_) return dw_tma_launch<K_, S_, TH_, NC_>(pl, s)
+  DW_CASE(3, 1, 8, 1); DW_CASE(3, 1, 7, 1); DW_CASE(3, 2, 8, 1); DW_CASE(3, 2, 7, 1);
+  DW_CASE(5, 1, 8, 1); DW_CASE(5, 1, 7, 1); DW_CASE(5, 2, 8, 1); DW_CASE(5, 2, 7, 1);
+  DW_CASE(3, 1, 8, 2); DW_CASE(3, 1, 7, 2); DW_CASE(5, 1, 7, 2);
 #undef DW_CASE
   return cudaErrorInvalidValue;
 }

@@ -259,10 +259,15 @@ int choose_bn(int cout, int* cout_pad) {
   }
   // several N tiles: the epilogue's 64-column TMA-store boxes must not reach into the next tile's
   // columns, so the N tile is a multiple of 64 (padded weight rows are zero, padded columns are clipped)
-  int t = (pad + 255) / 256;
-  int bn = ((pad + t - 1) / t + 63) / 64 * 64;
-  *cout_pad = bn * t;
-  return bn;
+  // Among 256 / 192 / 128 pick the tile with the least padded columns (ties: the wider one): 1152 -> 6 x 192
+  // exactly instead of 5 x 256 = 1280 (10 % dead columns and a worse wave count at 98 M tiles).
+  int best_bn = 256, best_pad = (pad + 255) / 256 * 256;
+  for (int bn = 192; bn >= 128; bn -= 64) {
+    const int p2 = (pad + bn - 1) / bn * bn;
+    if (p2 < best_pad) { best_pad = p2; best_bn = bn; }
+  }
+  *cout_pad = best_pad;
+  return best_bn;
 }
 
 struct PwOff { size_t w, bias; };

@@ -63,7 +63,7 @@ struct DwTmaParams {
   int cb_fixed;          // gridDim.x % ncb == 0: a CTA's tiles all share one channel block
   int gimg;              // images per tile (the box spans gimg images; small-spatial layers)
   int img_bytes;         // bytes of one image's box inside a stage
-  int inv_cp, inv_per_img;  // ceil(65536 / col_pairs), ceil(65536 / (col_pairs * strips))
+  int inv_cp, inv_per_img;  // ceil(65536 / col_groups), ceil(65536 / (col_groups * strips)); col_groups = otw / (2 NC)
   uint32_t box_bytes;
   int stage_stride;      // bytes between the two smem stages (1024-aligned)
   const float* wgt;      // [k*k, C] fp32, BN folded
@@ -91,6 +91,7 @@ struct DwPlan {
   DwTcParams q;
   int tc = 0;            // 1: planned for the tensor-core kernel
   int k = 0, stride = 0, th = 0;
+  int nc = 1;            // output columns per thread (2: big stride-1 layers, columns x and x+2 share loaded inputs)
   int grid = 0, block = 0;
   size_t smem = 0;
   const void* x = nullptr;  // cache key

@@ -290,7 +290,8 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   } else if (warp >= 4 && warp < 4 + (kGate ? kEpiWarps : kEpiWarpsWide)) {
     // ================= epilogue (group = accumulator; ungated: two column-half teams per group) =================
     constexpr int kHalves = kGate ? 1 : 2;   // teams of 4 warps per accumulator, alternating 64-column blocks
-    constexpr int kBufs = kGate ? 2 : 1;     // staging tiles per warp (64 KB of staging either way)
+    constexpr int kBufs = kGate ? 2 : 1;     // 4-KB staging areas per warp (64 KB of staging either way)
+    constexpr int kNB = 2 * kBufs;           // ... used as 2-KB buffers of one [32 x 32-column] store box each
     const int ew = warp - 4;
     const int grp = ew / (4 * kHalves);
     const int half = (ew >> 2) % kHalves;
@@ -318,14 +319,14 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
       for (int cb = half * 64; cb < p.bn; cb += 64 * kHalves) {
         const int ncols = min(64, p.bn - cb);  // multiple of 16
-        uint8_t* stg = stg_base + (stores % kBufs) * kEpiStageBytes;
-        if (stores >= kBufs) {  // the store that last used this staging tile must have finished READING it
-          PROF_WAIT(1, if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kBufs - 1) : "memory");
-                    __syncwarp())
-        }
 #pragma unroll
-        for (int hb = 0; hb < 2; ++hb) {  // two 32-column halves of the 64-column staging tile
+        for (int hb = 0; hb < 2; ++hb) {  // two 32-column halves, each with its own staging buffer and TMA store
           if (hb * 32 < ncols) {
+            uint8_t* stg = stg_base + (stores % kNB) * (kEpiStageBytes / 2);
+            if (stores >= kNB) {  // the store that last used this staging buffer must have finished READING it
+              PROF_WAIT(1, if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kNB - 1) : "memory");
+                        __syncwarp())
+            }
             const int col = ncol0 + cb + hb * 32;  // global output column of r[0]
             uint32_t r[32];
             tmem_ld32(t_row + (uint32_t)(cb + hb * 32), r);
@@ -384,24 +385,25 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               f2_unpack(v[4 * c + 1], a0, a1); pk.y = pack_bf16x2(a0, a1);
               f2_unpack(v[4 * c + 2], a0, a1); pk.z = pack_bf16x2(a0, a1);
               f2_unpack(v[4 * c + 3], a0, a1); pk.w = pack_bf16x2(a0, a1);
-              const int chunk = hb * 4 + c;
-              *reinterpret_cast<uint4*>(stg + lane * 128 + ((chunk ^ (lane & 7)) << 4)) = pk;
+              // [32 rows x 64 B] staging tile in the 64-B swizzle of the store's tensor map
+              *reinterpret_cast<uint4*>(stg + lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4)) = pk;
             }
+            // staging buffer -> global: one TMA store of the [32 rows x 32 cols] box (rows past the image and
+            // columns >= cout are clipped by the tensor map; columns past `ncols` only exist when they are
+            // >= cout, see choose_bn)
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && !(p.debug & 1)) {
+              asm volatile(
+                  "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                      reinterpret_cast<uint64_t>(&tmap_out)),
+                  "r"(smem_u32(stg)), "r"(col), "r"(lrow0), "r"(img)
+                  : "memory");
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            ++stores;
           }
         }
-        // staging tile -> global: one TMA store of the [32 rows x 64 cols] box (rows past the image and columns
-        // >= cout are clipped by the tensor map; columns past `ncols` only exist when they are >= cout, see choose_bn)
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0 && !(p.debug & 1)) {
-          asm volatile(
-              "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
-                  reinterpret_cast<uint64_t>(&tmap_out)),
-              "r"(smem_u32(stg)), "r"(ncol0 + cb), "r"(lrow0), "r"(img)
-              : "memory");
-          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        }
-        ++stores;
       }
     }
     if (ew == 0) { PROF_END(2) }
@@ -515,8 +517,12 @@ int encode_tmap_act_bf16(void* tmap_out, const void* base, long long m, int cols
   if (m <= 0 || m % rpi || (cols % 8) || box_rows > 256) return -2;
   unsigned long long dims[3] = {(unsigned long long)cols, (unsigned long long)rpi, (unsigned long long)(m / rpi)};
   unsigned long long str[3] = {2, (unsigned long long)cols * 2, (unsigned long long)rpi * cols * 2};
-  unsigned box[3] = {(unsigned)kBK, (unsigned)box_rows, 1};
-  return encode_tmap_nd_bf16(tmap_out, base, 3, dims, str, box, 128);
+  // box_rows == 128: operand tiles, 64 columns (128-B rows, 128-B swizzle)
+  // box_rows == 32 : epilogue store boxes, 32 columns (64-B rows, 64-B swizzle) -- half a 64-column block, so
+  //                  that a warp's two staging buffers alternate inside one block
+  const bool store_box = box_rows == 32;
+  unsigned box[3] = {(unsigned)(store_box ? 32 : kBK), (unsigned)box_rows, 1};
+  return encode_tmap_nd_bf16(tmap_out, base, 3, dims, str, box, store_box ? 64 : 128);
 }
 
 static size_t tc_smem_bytes(int bn, int stages, size_t bres_bytes) {
