@@ -44,6 +44,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200df_head": (_i, [_vp, _vp, _i, _vp, _vp]),
     "b200df_head_backward": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "b200df_softmax_pack": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
+    "b200df_cam_overlay": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, C.c_float, _vp, _vp]),
     "b200df_threshold_hist": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp]),
     "b200df_confusion_matrix": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "b200df_auc_counts": (_i, [_vp, _i, _vp, _i, _vp, _vp]),

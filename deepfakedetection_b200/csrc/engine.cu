@@ -765,6 +765,19 @@ extern "C" int b200df_softmax_pack(const float* logits, const int64_t* labels, i
   return B200DF_OK;
 }
 
+// ---- Grad-CAM overlay (web_ui.py:72-93, 281-282) ---------------------------------------------------------------
+extern "C" int b200df_cam_overlay(const float* images, const float* cam, int n, int h, int w, int denorm,
+                                  const float* mean, const float* stdv, float image_weight, unsigned char* out,
+                                  void* stream) {
+  if (n < 0 || h < 1 || w < 1 || (long long)h * w > (1 << 28) || !mean || !stdv || (n > 0 && (!images || !cam || !out)))
+    return fail(B200DF_E_INVALID, "bad argument");
+  if (!(image_weight >= 0.f && image_weight <= 1.f))
+    return fail(B200DF_E_INVALID, "image_weight should be in the range [0, 1]");
+  CU_OK(launch_cam_overlay(images, cam, n, h, w, denorm, mean, stdv, image_weight, out,
+                           reinterpret_cast<cudaStream_t>(stream)));
+  return B200DF_OK;
+}
+
 // ---- on-device metrics tail (orchestrator.py:536-546, 605-631) ------------------------------------------------
 extern "C" int b200df_threshold_hist(const float* scores, const int64_t* labels, int n, const double* thresholds,
                                      int nthr, long long* hist, void* stream) {

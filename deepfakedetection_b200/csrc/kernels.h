@@ -163,6 +163,10 @@ cudaError_t launch_softmax_pack(const float* logits, const int64_t* labels, int 
                                 cudaStream_t s);
 
 // on-device metrics tail (metrics.cu)
+// Grad-CAM overlay (overlay.cu): de-normalise + JET heat map + blend + max-normalise -> uint8 HWC
+cudaError_t launch_cam_overlay(const float* x_nchw, const float* cam, int n, int h, int w, int denorm, const float* mean,
+                               const float* stdv, float image_weight, unsigned char* out, cudaStream_t s);
+
 cudaError_t launch_threshold_hist(const float* scores, const int64_t* labels, int n, const double* thr, int nthr,
                                   unsigned long long* hist, cudaStream_t s);
 cudaError_t launch_confusion(const int64_t* targets, const int64_t* preds, int n, int nc, unsigned long long* cm,

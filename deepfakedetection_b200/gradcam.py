@@ -146,3 +146,35 @@ def show_cam_on_image(img: np.ndarray, mask: np.ndarray, use_rgb: bool = False, 
     cam = (1 - image_weight) * heat + image_weight * img
     cam = cam / np.max(cam)
     return np.uint8(255 * cam)
+
+
+def show_cam_on_image_device(images: torch.Tensor, cams: torch.Tensor, normalize: bool = True,
+                             mean=(0.485, 0.456, 0.406), std=(0.229, 0.224, 0.225),
+                             image_weight: float = 0.5) -> torch.Tensor:
+    """``_tensor_to_rgb(tensor, normalize=...)`` + ``show_cam_on_image(rgb, cam, use_rgb=True)`` for a whole batch
+    on the GPU (/root/reference/web_ui.py:72-93, 281-282): ``images`` float32 [N,3,H,W] (what the model saw),
+    ``cams`` float32 [N,H,W] in [0,1] -> uint8 [N,H,W,3] RGB overlays, byte-identical to the host functions."""
+    import ctypes as C
+
+    from . import _lib
+
+    if images.dim() != 4 or images.shape[1] != 3 or cams.dim() != 3 or cams.shape[0] != images.shape[0] \
+            or tuple(cams.shape[1:]) != tuple(images.shape[2:]):
+        raise ValueError("expected images [N,3,H,W] and cams [N,H,W]")
+    if not images.is_cuda or not cams.is_cuda:
+        raise RuntimeError("show_cam_on_image_device needs CUDA tensors (the host path is show_cam_on_image)")
+    if not 0 <= image_weight <= 1:
+        raise ValueError("image_weight should be in the range [0, 1]")
+    x = images.detach().float().contiguous()
+    m = cams.detach().float().contiguous()
+    n, _, h, w = x.shape
+    out = torch.empty((n, h, w, 3), dtype=torch.uint8, device=x.device)
+    mean_c = (C.c_float * 3)(*[float(v) for v in mean])
+    std_c = (C.c_float * 3)(*[float(v) for v in std])
+    with torch.cuda.device(x.device):
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        _lib.check(_lib.lib().b200df_cam_overlay(C.c_void_p(x.data_ptr()), C.c_void_p(m.data_ptr()), n, h, w,
+                                                  1 if normalize else 0, C.cast(mean_c, C.c_void_p),
+                                                  C.cast(std_c, C.c_void_p), C.c_float(image_weight),
+                                                  C.c_void_p(out.data_ptr()), stream))
+    return out

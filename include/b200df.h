@@ -120,6 +120,15 @@ int b200df_head_backward(b200df_handle h, const float* a_nchw, const float* grad
 int b200df_softmax_pack(const float* logits, const int64_t* labels, int n, int num_classes,
                         float* packed, void* stream);
 
+/* Grad-CAM overlay on the device: `_tensor_to_rgb(tensor, normalize)` (web_ui.py:72-93) followed by
+ * pytorch-grad-cam `show_cam_on_image(rgb, cam, use_rgb=True, image_weight)` (web_ui.py:281-282).
+ * images: float32 [n,3,h,w] NCHW (the tensor the model saw); cam: float32 [n,h,w] in [0,1];
+ * denorm != 0: rgb = images * std + mean first (mean/std: 3 host floats each); out: uint8 [n,h,w,3] RGB.
+ * Same separately-rounded fp32 operations as the numpy code: byte-identical to the host path. */
+int b200df_cam_overlay(const float* images, const float* cam, int n, int h, int w, int denorm,
+                       const float* mean, const float* stdv, float image_weight, unsigned char* out,
+                       void* stream);
+
 /* ---- on-device metrics tail (the counting work behind orchestrator.py:536-546 and :605-631) ---- */
 /* Threshold sweep: hist[cls*(nthr+1) + j] += #{samples of class cls (label==1 -> 1, else 0) whose float32
  * score, promoted to double, is >= exactly j of the ascending `thresholds`} -- so for threshold k,

@@ -301,3 +301,32 @@ def test_device_metrics_tail_matches_sklearn(case):
     t5 = torch.randint(0, 5, (3000,), device="cuda")
     p5 = torch.randint(0, 5, (3000,), device="cuda")
     np.testing.assert_array_equal(confusion_matrix_device(t5, p5, 5), confusion_matrix(t5.cpu().numpy(), p5.cpu().numpy(), labels=list(range(5))))
+
+
+def _tensor_to_rgb_like_web_ui(t: torch.Tensor, normalize: bool) -> np.ndarray:
+    """/root/reference/web_ui.py:72-93 restated on the host (torch CPU ops, float32)."""
+    arr = t.detach().clone()
+    if normalize:
+        mean = torch.tensor([0.485, 0.456, 0.406], dtype=arr.dtype)
+        std = torch.tensor([0.229, 0.224, 0.225], dtype=arr.dtype)
+        arr = arr * std.view(-1, 1, 1) + mean.view(-1, 1, 1)
+    return arr.clamp(0.0, 1.0).permute(1, 2, 0).numpy().astype(np.float32)
+
+
+@pytest.mark.parametrize("normalize", [True, False])
+@pytest.mark.parametrize("weight", [0.5, 0.3])
+def test_device_overlay_is_byte_identical_to_host_overlay(normalize, weight):
+    """web_ui.py:281-282: `_tensor_to_rgb` + `show_cam_on_image(rgb, cam, use_rgb=True)` on the GPU."""
+    from deepfakedetection_b200.gradcam import show_cam_on_image, show_cam_on_image_device
+
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(3, 3, 224, 224, generator=g) * (1.3 if normalize else 0.6) + (0.0 if normalize else 0.4)
+    cam = torch.rand(3, 224, 224, generator=g)
+    cam[0, :8] = 0.0
+    cam[1, -8:] = 1.0
+    dev = show_cam_on_image_device(x.cuda(), cam.cuda(), normalize=normalize, image_weight=weight).cpu().numpy()
+    for i in range(3):
+        rgb = _tensor_to_rgb_like_web_ui(x[i], normalize)
+        host = show_cam_on_image(rgb, cam[i].numpy(), use_rgb=True, image_weight=weight)
+        assert dev[i].shape == host.shape and dev[i].dtype == np.uint8
+        assert np.array_equal(dev[i], host), f"image {i}: {(dev[i] != host).sum()} bytes differ"
