@@ -199,11 +199,11 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   if (warp == 0 || warp == 2 || warp == 3) {
     // ================= TMA producers (up to three warps, one lane each) =================
-    // A lone lane needs ~1000 cycles of dependent uniform-datapath instructions per TMA issue (measured: the
-    // single producer never waited on an `empty` barrier -- it WAS the critical path of the thin layers), so
-    // the flattened (tile, K chunk) sequence is dealt round-robin to p.np producer lanes.  p.stages is a
-    // multiple of p.np, hence every ring slot has exactly ONE producer and the parity waits stay unambiguous
-    // (a producer two ring revolutions ahead of another on the same slot would alias mbarrier phases).
+    // The flattened (tile, K chunk) sequence is dealt round-robin to p.np producer lanes.  p.stages is a multiple
+    // of p.np, hence every ring slot has exactly ONE producer and the parity waits stay unambiguous (a producer
+    // two ring revolutions ahead of another on the same slot would alias mbarrier phases).  Measured: with the
+    // warp-uniform loop one lane already keeps the ring full (it waits on `empty` 60-90 % of the time); the
+    // extra lanes only matter for the thinnest tiles.
     const int pw = warp == 0 ? 0 : warp - 1;
     if (pw < p.np) {
       if (p.b_res && pw == 0 && elect_one()) {  // whole weight matrix, once per CTA (148 CTAs re-reading the
