@@ -38,6 +38,7 @@ constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kABytes = kBM * kBK * 2;  // 16 KB
 constexpr int kMaxStages = 8;
+constexpr int kScalWarps = 8;             // gated kernels: SE-gate scaler warps (the bottleneck role of the K-heavy 14^2 / 7^2 layers)
 constexpr int kEpiWarps = 8;              // gated kernels: two groups of four (one group per TMEM accumulator)
 constexpr int kEpiWarpsWide = 16;         // ungated kernels (expand, conv_head: wide N, SiLU): two column halves per group
 constexpr int kEpiStageBytes = 32 * 128;  // one staging tile: 32 rows x 64 bf16; TWO per epilogue warp
@@ -51,6 +52,7 @@ struct TcParams {
   int b_res;          // scale_b only: the pristine weight matrix (all K chunks) stays resident in shared memory
   int prof_slot;      // TC_PROF builds: row of g_tc_prof this launch writes
   int np;             // TMA producer lanes (1..3); stages % np == 0
+  int sg;             // gated: scaler groups (1, 2 or 4); stages % sg == 0
   int b_once;         // weights fit one (k chunk, n tile): load the B tile once per ring slot, not per tile
   int debug;          // B200DF_TC_DEBUG bits (experiments only): 1 = skip the output stores
   int scale_b;        // gated only: 1 = fold the gate into the B (weight) tile, 0 = into the A tile
@@ -141,7 +143,7 @@ struct TileIter {
 };
 
 template <bool kGate, int kAct, bool kRes>
-__global__ void __launch_bounds__(kGate ? 512 : 640, 1)
+__global__ void __launch_bounds__(640, 1)
 pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_out, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -151,7 +153,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int stage_bytes = kABytes + b_bytes;
   uint8_t* bres = smem + (size_t)p.stages * stage_bytes;      // 1024-aligned: stage_bytes % 1024 == 0
   uint8_t* epi_smem = bres + (p.b_res ? (size_t)p.k_chunks * b_bytes : 0);
-  float* sbias = reinterpret_cast<float*>(epi_smem + 2 * kEpiWarps * kEpiStageBytes);
+  float* sbias = reinterpret_cast<float*>(epi_smem + (kGate ? 1 : 2) * kEpiWarps * kEpiStageBytes);
   float* sgate = sbias + kMaxBiasFloats;  // [stages][64] fp32: the SE gate slice of every ring slot's (image, K chunk)
   uint64_t* bars = reinterpret_cast<uint64_t*>(sgate + kMaxStages * kBK);
   uint64_t* full_bar = bars;
@@ -176,7 +178,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
-      mbar_init(&scaled_bar[s], 4);  // one arrival per scaler warp
+      mbar_init(&scaled_bar[s], kScalWarps / p.sg);  // one arrival per warp of the group that owns the chunk
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
@@ -290,7 +292,7 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   } else if (warp >= 4 && warp < 4 + (kGate ? kEpiWarps : kEpiWarpsWide)) {
     // ================= epilogue (group = accumulator; ungated: two column-half teams per group) =================
     constexpr int kHalves = kGate ? 1 : 2;   // teams of 4 warps per accumulator, alternating 64-column blocks
-    constexpr int kBufs = kGate ? 2 : 1;     // 4-KB staging areas per warp (64 KB of staging either way)
+    constexpr int kBufs = 1;                 // one 4-KB staging area per warp (gated: 32 KB, ungated: 64 KB)
     constexpr int kNB = 2 * kBufs;           // ... used as 2-KB buffers of one [32 x 32-column] store box each
     const int ew = warp - 4;
     const int grp = ew / (4 * kHalves);
@@ -416,59 +418,69 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     //   else   : A tile [rows x 64] (activations) *= gate -- only the image's valid rows
     // A thread owns ONE 16-byte K chunk (8 channels): its 8 fp32 gate values come from the ring slot's gate
     // slice (bulk-copied by the producer on the same barrier as the tile) and stay in registers for all of
-    // its rows (rows ts/8, ts/8 + 16, ...).
-    const int ts = threadIdx.x - 32 * (4 + kEpiWarps);
+    // its rows (rows ts/8, ts/8 + 32, ...).
+    // The warps form kScalGroups groups that take the (tile, K chunk) sequence in turn: a chunk's path through
+    // a scaler (barrier wait -> gate + tile loads -> multiply -> stores -> proxy fence -> arrive) is one
+    // dependent chain of ~900 cycles whatever the row count, so what matters is how many chunks are in
+    // flight, not how many threads share one chunk.
+    const int kScalGroups = p.sg;                        // every ring slot belongs to ONE group (stages % sg == 0)
+    const int kTG = 32 * kScalWarps / kScalGroups;       // threads per group
+    const int kRowsPass = kTG / 8;                       // rows covered by one pass of a group (16 or 32)
+    const int tsa = threadIdx.x - 32 * (4 + kEpiWarps);
+    const int sgrp = tsa / kTG;
+    const int ts = tsa - sgrp * kTG;
     const int lc = ts & 7;          // logical 16-B chunk inside the 128-B swizzled row
-    const int rg = ts >> 3;         // first row; rows rg + 16 j
-    const int pc = lc ^ (rg & 7);   // physical chunk ((rg + 16 j) & 7 == rg & 7)
-    int s = 0;
-    uint32_t ph = 0;
+    const int rg = ts >> 3;         // first row; rows rg + kRowsPass * j
+    const int pc = lc ^ (rg & 7);   // physical chunk (kRowsPass % 8 == 0: every row of this thread has rg & 7)
     PROF_DECL
     PROF_WAIT(1, if (p.b_res) mbar_wait(bres_bar, 0))
-    // (n tile, M sub-tile, image) of the current tile, advanced by the grid stride in mixed radix: a lone warp
-    // per scheduler runs at ~0.2 IPC, so there are no divisions and as few instructions as possible per tile
+    // (n tile, M sub-tile, image) of the current tile, advanced by the grid stride in mixed radix (no divisions)
     TileIter ti(t_begin, t_step, p.n_tiles, p.tiles_per_img);
     const int kq_max = p.cin >> 3;
-    for (int t = t_begin; t < t_end; t += t_step, ti.next()) {
-      const int lrow0 = ti.sub * kBM;
-      const int nrows = p.scale_b ? p.bn : min(kBM, p.rpi - lrow0);  // rows of the tile to scale
-      for (int kc = 0; kc < p.k_chunks; ++kc) {
-        const bool k_ok = kc * (kBK / 8) + lc < kq_max;
-        PROF_WAIT(0, mbar_wait(&full_bar[s], ph))
-        PROF_BEGIN
-        if (k_ok) {
-          const float4* sg = reinterpret_cast<const float4*>(sgate + s * kBK) + 2 * lc;
-          const float4 g0 = sg[0], g1 = sg[1];
-          uint8_t* base = smem + (size_t)s * stage_bytes + (p.scale_b ? kABytes : 0) + rg * 128 + (pc << 4);
-          // source: the tile itself (scaled in place) or the resident pristine weights
-          const uint8_t* src = p.b_res ? bres + (size_t)kc * b_bytes + rg * 128 + (pc << 4) : base;
-          for (int r0 = rg; r0 < nrows; r0 += 64, base += 64 * 128, src += 64 * 128) {
-            uint4 a[4];
+    int s = sgrp;                   // ring slot of this group's next chunk (kScalGroups <= stages)
+    uint32_t ph = 0;
+    int kc = sgrp, t = t_begin;
+    while (kc >= p.k_chunks) { kc -= p.k_chunks; t += t_step; ti.next(); }
+    while (t < t_end) {
+      const int nrows = p.scale_b ? p.bn : min(kBM, p.rpi - ti.sub * kBM);  // rows of the tile to scale
+      const bool k_ok = kc * (kBK / 8) + lc < kq_max;
+      PROF_WAIT(0, mbar_wait(&full_bar[s], ph))
+      PROF_BEGIN
+      if (k_ok) {
+        const float4* sg = reinterpret_cast<const float4*>(sgate + s * kBK) + 2 * lc;
+        const float4 g0 = sg[0], g1 = sg[1];
+        uint8_t* base = smem + (size_t)s * stage_bytes + (p.scale_b ? kABytes : 0) + rg * 128 + (pc << 4);
+        // source: the tile itself (scaled in place) or the resident pristine weights
+        const uint8_t* src = p.b_res ? bres + (size_t)kc * b_bytes + rg * 128 + (pc << 4) : base;
+        for (int r0 = rg; r0 < nrows; r0 += 4 * kRowsPass, base += 4 * kRowsPass * 128, src += 4 * kRowsPass * 128) {
+          uint4 a[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-              if (r0 + 16 * j < nrows) a[j] = *reinterpret_cast<const uint4*>(src + j * 16 * 128);
+          for (int j = 0; j < 4; ++j)
+            if (r0 + kRowsPass * j < nrows) a[j] = *reinterpret_cast<const uint4*>(src + j * kRowsPass * 128);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              if (r0 + 16 * j < nrows) {
-                a[j].x = scale_bf16x2(a[j].x, g0.x, g0.y);
-                a[j].y = scale_bf16x2(a[j].y, g0.z, g0.w);
-                a[j].z = scale_bf16x2(a[j].z, g1.x, g1.y);
-                a[j].w = scale_bf16x2(a[j].w, g1.z, g1.w);
-                *reinterpret_cast<uint4*>(base + j * 16 * 128) = a[j];
-              }
+          for (int j = 0; j < 4; ++j) {
+            if (r0 + kRowsPass * j < nrows) {
+              a[j].x = scale_bf16x2(a[j].x, g0.x, g0.y);
+              a[j].y = scale_bf16x2(a[j].y, g0.z, g0.w);
+              a[j].z = scale_bf16x2(a[j].z, g1.x, g1.y);
+              a[j].w = scale_bf16x2(a[j].w, g1.z, g1.w);
+              *reinterpret_cast<uint4*>(base + j * kRowsPass * 128) = a[j];
             }
           }
-          PROF_LAP(2)
-          fence_proxy_async_smem();
-          PROF_LAP(3)
         }
-        __syncwarp();  // every lane's writes + proxy fence precede the warp's single arrival
-        if (lane == 0) mbar_arrive(&scaled_bar[s]);
-        PROF_LAP(4)
-        if (++s == p.stages) { s = 0; ph ^= 1; }
+        PROF_LAP(2)
+        fence_proxy_async_smem();
+        PROF_LAP(3)
       }
+      __syncwarp();  // every lane's writes + proxy fence precede the warp's single arrival
+      if (lane == 0) mbar_arrive(&scaled_bar[s]);
+      PROF_LAP(4)
+      s += kScalGroups;
+      if (s >= p.stages) { s -= p.stages; ph ^= 1; }
+      kc += kScalGroups;
+      while (kc >= p.k_chunks) { kc -= p.k_chunks; t += t_step; ti.next(); }
     }
-    if (ts < 32) { PROF_END(3) }
+    if (tsa < 32) { PROF_END(3) }
   }
 
   tcgen05_fence_before();
@@ -525,9 +537,9 @@ int encode_tmap_act_bf16(void* tmap_out, const void* base, long long m, int cols
   return encode_tmap_nd_bf16(tmap_out, base, 3, dims, str, box, store_box ? 64 : 128);
 }
 
-static size_t tc_smem_bytes(int bn, int stages, size_t bres_bytes) {
+static size_t tc_smem_bytes(int bn, int stages, size_t bres_bytes, bool gated) {
   return 1024 /*align slack*/ + (size_t)stages * (kABytes + bn * kBK * 2) + bres_bytes +
-         2 * kEpiWarps * kEpiStageBytes + (kMaxBiasFloats + kMaxStages * kBK) * sizeof(float) +
+         (gated ? 1 : 2) * kEpiWarps * kEpiStageBytes + (kMaxBiasFloats + kMaxStages * kBK) * sizeof(float) +
          (3 * kMaxStages + 5) * sizeof(uint64_t) + 16;
 }
 
@@ -569,7 +581,8 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   p.b_res = (p.scale_b && bres_bytes <= 40 * 1024 && !(dbg & 4)) ? 1 : 0;
   if (!p.b_res) bres_bytes = 0;
   int stages = kMaxStages;
-  while (stages > 2 && tc_smem_bytes(a.bn, stages, bres_bytes) > budget) --stages;
+  const bool gated = a.gate != nullptr;
+  while (stages > 2 && tc_smem_bytes(a.bn, stages, bres_bytes, gated) > budget) --stages;
   if (p.b_res && p.k_chunks <= stages) stages = stages / p.k_chunks * p.k_chunks;  // slot <-> K chunk mapping fixed
   // producer lanes: every ring slot must belong to one producer (stages % np == 0)
   static int np_max = -1;
@@ -579,6 +592,18 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
     if (np_max < 1 || np_max > 3) np_max = 3;
   }
   if (np_max >= 2 && !p.b_res && stages >= 5 && stages % 2 && stages % 3) --stages;  // 5 -> 4, 7 -> 6
+  // gated: two scaler groups alternate over the K chunks when every ring slot can belong to one group
+  if (gated && stages % 2 && stages >= 5 && !(p.b_res && p.k_chunks <= stages && (stages - 1) % p.k_chunks)) --stages;
+  p.sg = (gated && stages % 2 == 0) ? 2 : 1;
+  {
+    static int sg_max = -1;
+    if (sg_max < 0) {
+      const char* e = getenv("B200DF_TC_SG");
+      sg_max = e ? atoi(e) : 2;
+    }
+    if (gated && sg_max >= 4 && stages % 4 == 0) p.sg = 4;
+    if (sg_max == 1) p.sg = 1;
+  }
   p.np = (np_max >= 3 && stages % 3 == 0) ? 3 : ((np_max >= 2 && stages % 2 == 0) ? 2 : 1);
   p.stages = stages;
 #ifdef TC_PROF
@@ -591,14 +616,14 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   p.bias = a.bias;
   p.gate = a.gate;
   p.residual = reinterpret_cast<const bf16*>(a.residual);
-  const size_t smem = tc_smem_bytes(a.bn, stages, bres_bytes);
+  const size_t smem = tc_smem_bytes(a.bn, stages, bres_bytes, gated);
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
   const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
   const CUtensorMap* ta = reinterpret_cast<const CUtensorMap*>(a.tmap_a);
   const CUtensorMap* tb = reinterpret_cast<const CUtensorMap*>(a.tmap_b);
   const CUtensorMap* to = reinterpret_cast<const CUtensorMap*>(a.tmap_out);
   const bool res = a.residual != nullptr;
-  const int threads = a.gate ? 512 : 640;
+  const int threads = 640;  // gated: 4 + 8 epilogue + 8 scaler warps; ungated: 4 + 16 epilogue warps
 #define TC_LAUNCH(G_, A_, R_)                                                                                  \
   if ((a.gate != nullptr) == G_ && a.act == A_ && res == R_) {                                                 \
     static bool attr_done = false;                                                                             \
