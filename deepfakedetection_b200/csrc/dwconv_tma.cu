@@ -69,6 +69,7 @@ __device__ __forceinline__ f32x2 bf16x2_to_f32x2(uint32_t raw) {
 
 struct DwTile { int cb, tx, ty, ng; };
 
+// (Three CTAs per SM for the 3x3 single-column variants -- 80 registers, <= 74 KB plans -- measured slower.)
 template <int K, int S, int TH, int NC>
 __global__ void __launch_bounds__(256, 2)
 dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p) {
@@ -362,7 +363,16 @@ int dw_tma_occupancy_dispatch(int k, int stride, int th, int nc, int block, size
   return 1;
 }
 
-constexpr size_t kDwSmemLimit = 110 * 1024;  // per CTA (2 operand stages + pool slots) -> 2 CTAs per SM
+constexpr size_t kDwSmemLimitDefault = 110 * 1024;  // per CTA (2 operand stages + pool slots) -> 2 CTAs per SM
+static size_t dw_smem_limit() {  // B200DF_DW_SMEM_KB: sweep aid (e.g. 74 -> plans that allow 3 CTAs per SM)
+  static size_t v = 0;
+  if (!v) {
+    const char* e = getenv("B200DF_DW_SMEM_KB");
+    v = e ? (size_t)atoi(e) * 1024 : kDwSmemLimitDefault;
+  }
+  return v;
+}
+#define kDwSmemLimit dw_smem_limit()
 
 }  // namespace
 

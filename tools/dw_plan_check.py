@@ -13,7 +13,7 @@ P = lambda t: C.c_void_p(t.data_ptr())
 CASES = [(112, 32, 3, 1, "7,16,4,1,2"), (112, 96, 3, 2, "7,14,1,1,1"), (56, 144, 3, 1, "7,8,8,1,2"),
          (56, 144, 5, 2, "7,4,4,1,1"), (28, 240, 5, 1, "7,4,4,1,2"), (14, 672, 5, 2, "7,8,1,1,1"),
          (7, 1152, 5, 1, "7,8,1,4,2"), (7, 1152, 3, 1, "7,8,1,4,2"), (7, 1152, 5, 1, "7,8,1,2,2"),
-         (14, 480, 5, 1, "7,16,1,1,2")]
+         (14, 480, 5, 1, "7,16,1,1,2"), (14, 480, 3, 1, "7,16,2,2,2"), (28, 240, 3, 2, "7,8,1,1,1")]
 N = 6
 for (h, c, k, s, pin) in CASES:
     ho = (h + 2 * ((k - 1) // 2) - k) // s + 1

@@ -28,7 +28,7 @@ def run(xs, w, b, outs, pool, k, s, reps):
 
 for (h, c, k, s) in LAYERS:
     tag = f"{h}x{c}k{k}s{s}"
-    if only and only != "default" and only != tag:
+    if only and only != "default" and tag not in only.split(","):
         continue
     ho = (h + 2 * ((k - 1) // 2) - k) // s + 1
     nb = max(2, int(300e6 // (N * h * h * c * 2)) + 1)
