@@ -185,7 +185,9 @@ static bool stem_force_simt() {
 
 cudaError_t launch_stem(const float* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
                         int dtype, cudaStream_t s) {
-  if (dtype == kBF16 && !stem_force_simt()) return launch_stem_tc(x, n, h, w, wgt, bias, out, s);
+  // the tcgen05 stem gathers with 8-byte loads: images not 8-byte aligned take the SIMT kernel
+  if (dtype == kBF16 && !stem_force_simt() && (reinterpret_cast<uintptr_t>(x) & 7) == 0)
+    return launch_stem_tc(x, n, h, w, wgt, bias, out, s);
   if (dtype == kBF16) return stem_launch<bf16, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
   return stem_launch<float, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
 }

@@ -90,28 +90,55 @@ stem_tc_kernel(const void* __restrict__ xin, int n, int H, int W, const float* _
 #pragma unroll
     for (int k = 27; k < 32; ++k) f[k] = 0.f;
     const int ih0 = 2 * oh - 1, iw0 = 2 * ow - 1;
+    if constexpr (!kU8) {
+      // fp32 NCHW: taps kx = 1, 2 of a pixel are the aligned pair (2 ow, 2 ow + 1) -> one 8-byte load; tap kx = 0
+      // (2 ow - 1) is the second half of the LEFT neighbour's pair -> a shuffle from lane - 1.  Lanes whose left
+      // neighbour sits in another warp / row (lane 0, ow == 0) load it themselves (ow == 0: zero padding).
+      const float* x = reinterpret_cast<const float*>(xin);
+      const int lane = tid & 31;
+      const bool own_left = lane == 0 || ow == 0;   // the left neighbour is not lane - 1 of this row
+      float2 pr[9];
+      float own[9];
+      // all 18 loads first (predicated, no branches: they must all be in flight together), shuffles afterwards
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
+      for (int c = 0; c < 3; ++c) {
 #pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        const int ih = ih0 + ky;
-        const bool row_ok = valid && ih >= 0 && ih < H;
+        for (int ky = 0; ky < 3; ++ky) {
+          const int ih = ih0 + ky;
+          const bool row_ok = valid && ih >= 0 && ih < H;
+          const float* rowp = x + (((size_t)img * 3 + c) * H + (row_ok ? ih : 0)) * W;
+          pr[c * 3 + ky] = make_float2(0.f, 0.f);
+          own[c * 3 + ky] = 0.f;
+          if (row_ok) pr[c * 3 + ky] = __ldg(reinterpret_cast<const float2*>(rowp + 2 * ow));
+          if (row_ok && own_left && ow > 0) own[c * 3 + ky] = __ldg(rowp + iw0);
+        }
+      }
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const int iw = iw0 + kx;
-          const bool ok = row_ok && iw >= 0 && iw < W;
-          float v = 0.f;
-          if constexpr (!kU8) {
-            const float* x = reinterpret_cast<const float*>(xin);
-            if (ok) v = __ldg(x + (((size_t)img * 3 + c) * H + ih) * W + iw);
-          } else {
+      for (int i = 0; i < 9; ++i) {
+        const float up = __shfl_up_sync(0xffffffffu, pr[i].y, 1);
+        f[i * 3 + 0] = own_left ? own[i] : up;
+        f[i * 3 + 1] = pr[i].x;
+        f[i * 3 + 2] = pr[i].y;
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+          const int ih = ih0 + ky;
+          const bool row_ok = valid && ih >= 0 && ih < H;
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const int iw = iw0 + kx;
+            const bool ok = row_ok && iw >= 0 && iw < W;
+            float v = 0.f;
             const uint8_t* x = reinterpret_cast<const uint8_t*>(xin);
             if (ok) {
               const float u = (float)__ldg(x + (((size_t)img * H + ih) * W + iw) * 3 + c);
               v = fmaf(u, c == 0 ? sc0 : (c == 1 ? sc1 : sc2), c == 0 ? sh0 : (c == 1 ? sh1 : sh2));
             }
+            f[c * 9 + ky * 3 + kx] = v;
           }
-          f[c * 9 + ky * 3 + kx] = v;
         }
       }
     }
