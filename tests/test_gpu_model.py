@@ -330,3 +330,36 @@ def test_device_overlay_is_byte_identical_to_host_overlay(normalize, weight):
         host = show_cam_on_image(rgb, cam[i].numpy(), use_rgb=True, image_weight=weight)
         assert dev[i].shape == host.shape and dev[i].dtype == np.uint8
         assert np.array_equal(dev[i], host), f"image {i}: {(dev[i] != host).sum()} bytes differ"
+
+
+def test_programmatic_dependent_launch_changes_no_bit():
+    """Every hot-path kernel starts under programmatic dependent launch (kernels.h: launch_pdl) and must not touch
+    an activation before its griddepcontrol.wait.  A kernel that did would race with its predecessor's tail; the
+    same forward with PDL switched off (fully serialised launches) must therefore give bit-identical logits."""
+    import os
+    import subprocess
+    import sys
+
+    code = (
+        "import torch, hashlib\n"
+        "from oracle.effnet_b0 import make_seeded_oracle, synth_images\n"
+        "from deepfakedetection_b200 import registry\n"
+        "ref = make_seeded_oracle(seed=0)\n"
+        "m = registry.get_model_spec('efficientnet_b0').builder('efficientnet_b0', 2)\n"
+        "m.to('cuda').eval(); m.load_state_dict(ref.state_dict(), strict=False)\n"
+        "x = synth_images(96, seed=5).cuda()\n"
+        "with torch.inference_mode():\n"
+        "    outs = [m(x).cpu() for _ in range(4)]\n"
+        "    lg, low, cam = m.forward_cam(x[:8], None)\n"
+        "assert all(torch.equal(outs[0], o) for o in outs)\n"
+        "h = hashlib.sha256(outs[0].numpy().tobytes() + low.cpu().numpy().tobytes()).hexdigest()\n"
+        "print('DIGEST', h)\n"
+    )
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = []
+    for pdl in ("0", "1"):
+        env = dict(os.environ, B200DF_PDL=pdl, PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+        out = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0, out.stderr[-2000:]
+        digests.append([ln for ln in out.stdout.splitlines() if ln.startswith("DIGEST")][-1])
+    assert digests[0] == digests[1], "logits differ between serialised and programmatic-dependent launches"
