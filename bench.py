@@ -311,8 +311,9 @@ def run_b200(args) -> None:
 
 def run_e2e(model, step, B, K, W, dev, rank, world, local, u8: bool = False):
     """Host-resident fp32 NCHW batches (what the reference's DataLoader hands over, pin_memory=True,
-    orchestrator.py:386-395,588): every step copies its batch H2D (copy stream, double-buffered against
-    the compute stream, like `.to(device, non_blocking=True)`), runs the module, and reads the packed
+    orchestrator.py:386-395,588): every step copies its batch H2D (the package's HostBatchFeeder: two halves on
+    two copy streams, double-buffered against the compute stream -- `.to(device, non_blocking=True)` with both
+    copy engines busy), runs the module, and reads the packed
     probs/preds back D2H.  Timed with CUDA events on the compute stream, max over ranks."""
     import torch
     import torch.distributed as dist
@@ -321,29 +322,21 @@ def run_e2e(model, step, B, K, W, dev, rank, world, local, u8: bool = False):
 
     if u8:  # GPU-side input path: uint8 HWC crops, ToTensor + Normalize fused into the stem
         host = [torch.randint(0, 256, (B, 224, 224, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
-        dbuf = [torch.empty(B, 224, 224, 3, dtype=torch.uint8, device=dev) for _ in range(2)]
         step = model.forward_u8
     else:
         host = [torch.randn(B, 3, 224, 224).pin_memory() for _ in range(2)]
-        dbuf = [torch.empty(B, 3, 224, 224, device=dev) for _ in range(2)]
     in_bytes = host[0].numel() * host[0].element_size()
     out_host = torch.empty(K + W, B, 4, dtype=torch.float32).pin_memory()
-    copy_s = torch.cuda.Stream(dev)
+    from deepfakedetection_b200.evaluate import HostBatchFeeder
+
+    feeder = HostBatchFeeder(host[0], dev, parts=2)   # the package's own H2D path: two halves on two copy streams
     comp_s = torch.cuda.current_stream(dev)
-    copied = [torch.cuda.Event() for _ in range(2)]
-    consumed = [torch.cuda.Event() for _ in range(2)]
 
     def loop(n, base):
         for i in range(n):
-            j = i & 1
-            with torch.cuda.stream(copy_s):
-                if i >= 2:
-                    copy_s.wait_event(consumed[j])
-                dbuf[j].copy_(host[j], non_blocking=True)
-                copied[j].record(copy_s)
-            comp_s.wait_event(copied[j])
-            rec = pack_records(step(dbuf[j]), None)
-            consumed[j].record(comp_s)
+            x = feeder.feed(i, host[i & 1])
+            rec = pack_records(step(x), None)
+            feeder.release(i)
             out_host[base + i].copy_(rec, non_blocking=True)
 
     loop(W, 0)
@@ -353,7 +346,7 @@ def run_e2e(model, step, B, K, W, dev, rank, world, local, u8: bool = False):
         torch.cuda.synchronize(dev)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(comp_s)
-    copy_s.wait_event(ev0)
+    feeder.wait_event_on_copy_streams(ev0)
     loop(K, W)
     ev1.record(comp_s)
     torch.cuda.synchronize(dev)
@@ -366,7 +359,7 @@ def run_e2e(model, step, B, K, W, dev, rank, world, local, u8: bool = False):
             "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": B * 4 * 4,
             "ms_per_step": round(ms / K, 4),
             "note": ("pinned uint8 HWC host batches (forward_u8)" if u8 else "pinned fp32 NCHW host batches") +
-                    ", H2D on a copy stream double-buffered with compute; h2d GB/s per GPU = %.1f"
+                    ", H2D in two halves on two copy streams (evaluate.HostBatchFeeder), double-buffered with compute; h2d GB/s per GPU = %.1f"
                     % (in_bytes * K / (ms * 1e-3) / 1e9)}
 
 

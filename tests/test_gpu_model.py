@@ -363,3 +363,21 @@ def test_programmatic_dependent_launch_changes_no_bit():
         assert out.returncode == 0, out.stderr[-2000:]
         digests.append([ln for ln in out.stdout.splitlines() if ln.startswith("DIGEST")][-1])
     assert digests[0] == digests[1], "logits differ between serialised and programmatic-dependent launches"
+
+
+def test_host_batch_feeder_delivers_every_batch_intact():
+    """evaluate.HostBatchFeeder = `.to(device, non_blocking=True)` over two copy streams, double-buffered."""
+    from deepfakedetection_b200.evaluate import HostBatchFeeder
+
+    g = torch.Generator().manual_seed(2)
+    hosts = [torch.randn(7, 3, 32, 32, generator=g).pin_memory() for _ in range(5)]
+    feeder = HostBatchFeeder(hosts[0], "cuda", parts=2)
+    sums = []
+    for i, h in enumerate(hosts):
+        x = feeder.feed(i, h)
+        sums.append((x.double().sum(), x[3, 1].clone()))   # consumer work on the compute stream
+        feeder.release(i)
+    torch.cuda.synchronize()
+    for (s, row), h in zip(sums, hosts):
+        assert abs(s.item() - h.double().sum().item()) < 1e-9
+        assert torch.equal(row.cpu(), h[3, 1])
