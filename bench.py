@@ -49,6 +49,9 @@ def parse_args() -> argparse.Namespace:
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--workload", choices=["eval", "cam"], default="eval")
     ap.add_argument("--precision", choices=["bf16", "fp32"], default="bf16")
+    ap.add_argument("--model", choices=["efficientnet_b0", "efficientnet_b3"], default="efficientnet_b0",
+                    help="efficientnet_b0 = BASELINE.json's headline (timm layout); efficientnet_b3 = the reference "
+                         "registry's default entry (efficientnet_pytorch layout, SURVEY 8f-2), an extra line")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -150,12 +153,14 @@ def peaks() -> tuple[dict, str]:
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
-def cpu_eval_images_per_s(state: dict, batch: int, steps: int, warmup: int, seed: int = 0):
+def cpu_eval_images_per_s(state: dict, batch: int, steps: int, warmup: int, seed: int = 0,
+                          arch: str = "efficientnet_b0"):
     """The reference eval-loop body (orchestrator.py:587-592) on the fp32 oracle port, host cores."""
     import torch
     from oracle.effnet_b0 import EfficientNetB0Oracle  # the checker: cpu_baseline / reference arm only
+    from oracle.effnet_b3 import EfficientNetB3Oracle
 
-    model = EfficientNetB0Oracle(2).eval()
+    model = (EfficientNetB3Oracle(2) if arch == "efficientnet_b3" else EfficientNetB0Oracle(2)).eval()
     model.load_state_dict(state, strict=False)
     g = torch.Generator().manual_seed(seed)
     x = torch.randn(batch, 3, 224, 224, generator=g)
@@ -181,20 +186,21 @@ def run_reference(args) -> None:
         return
     import torch
 
-    from deepfakedetection_b200.module import B200EfficientNetB0
+    from deepfakedetection_b200.module import B200EfficientNetB0, B200EfficientNetB3
 
-    m = B200EfficientNetB0(2, "fp32")
+    m = (B200EfficientNetB3 if args.model == "efficientnet_b3" else B200EfficientNetB0)(2, "fp32")
     synth_state(m)
     sample_batch = 64
-    ips, ms, cores = cpu_eval_images_per_s(m.state_dict(), sample_batch, args.steps, min(args.warmup, 3))
+    ips, ms, cores = cpu_eval_images_per_s(m.state_dict(), sample_batch, args.steps, min(args.warmup, 3),
+                                           arch=args.model)
     line = {
-        "impl": "reference", "metric": METRIC, "value": round(ips, 2), "unit": UNIT, "n_gpus": args.gpus,
+        "impl": "reference", "metric": METRIC.replace("efficientnet_b0", args.model), "value": round(ips, 2), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": min(args.warmup, 3), "ms_per_step": round(ms, 3), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "efficientnet_b0 eval forward 224x224, 2-class head, fp32 eager on host cores",
+        "config": {"workload": f"{args.model} eval forward 224x224, 2-class head, fp32 eager on host cores",
                    "batch_per_step": sample_batch, "torch_threads": cores},
         "cpu_baseline": {"value": round(ips, 2), "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{args.steps} steps x {sample_batch} images, oracle/effnet_b0.py fp32 eager "
+                         "sample": f"{args.steps} steps x {sample_batch} images, oracle/{args.model.replace('efficientnet', 'effnet')}.py fp32 eager "
                                    f"(timm not installable; os.cpu_count={os.cpu_count()})"},
         "e2e": {"value": round(ips, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -223,7 +229,7 @@ def run_b200(args) -> None:
             os.environ["NCCL_DEBUG"] = "WARN"   # NCCL prints its version banner to STDOUT; keep stdout = one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
-    name = "efficientnet_b0" if args.precision == "bf16" else "efficientnet_b0.b200_fp32"
+    name = args.model if args.precision == "bf16" else args.model + ".b200_fp32"
     model = registry.get_model_spec(name).builder(name, 2)   # the reference's builder(name, num_classes) call
     synth_state(model)
     model.to(dev).eval()
@@ -381,7 +387,7 @@ def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, 
     t_launch = t / cnt * 1e-3
     hbm_peak = float(pk["hbm_gbs"])
     achieved = by / cnt / t_launch / 1e9
-    traffic, traffic_src = ncu_traffic_per_launch(dom)
+    traffic, traffic_src = ncu_traffic_per_launch(dom) if args.model == "efficientnet_b0" else (None, None)  # ncu capture is B0's
     roofline = {"kernel": dom, "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
                 "frac": round(achieved / hbm_peak, 4), "traffic": None if traffic is None else round(traffic),
                 "traffic_source": traffic_src, "algorithmic_bytes_per_launch": round(by / cnt),
@@ -390,15 +396,18 @@ def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, 
                 "avg_launch_ms": round(t_launch * 1e3, 4)}
     es = 2 if args.precision == "bf16" else 4
     algo_gb = (ALGO_MB_PER_IMG * (es / 2) * B + WEIGHT_MB * (es / 2)) / 1e3
+    if args.model != "efficientnet_b0":  # sum of the per-launch algorithmic bytes the engine tags its launches with
+        algo_gb = sum(v[1] for v in per_class.values()) / reps / 1e9
     net = {"algorithmic_GB_per_step": round(algo_gb, 3), "achieved_GBps": round(algo_gb / (ms_step * 1e-3), 1),
            "frac_of_hbm_peak": round(algo_gb / (ms_step * 1e-3) / hbm_peak, 4),
            "profiled_ms_per_step": round(prof_ms, 4)}
     line = {
-        "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "metric": METRIC.replace("efficientnet_b0", args.model), "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": args.precision, "data": "synthetic",
-        "config": {"workload": ("efficientnet_b0 eval forward" if args.workload == "eval" else "efficientnet_b0 forward + fused Grad-CAM")
-                   + " 224x224, 2-class head (BASELINE.json configs[1])", "batch_per_gpu": B, "global_batch": B * world,
+        "config": {"workload": (f"{args.model} eval forward" if args.workload == "eval" else f"{args.model} forward + fused Grad-CAM")
+                   + " 224x224, 2-class head" + (" (BASELINE.json configs[1])" if args.model == "efficientnet_b0" else
+                                                 " (reference registry default, efficientnet_pytorch layout; SURVEY 8f-2)"), "batch_per_gpu": B, "global_batch": B * world,
                    "input": "float32 NCHW [B,3,224,224] resident in HBM", "l2": "inputs (154 MB/batch) and per-step "
                    "activations (>3 GB) exceed the 126 MB L2; no explicit flush",
                    "collective": "one all_gather of packed probs/preds/labels after the K steps (inside the timed region)",
@@ -411,9 +420,10 @@ def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, 
         line["e2e_u8"] = e2e_u8
     if not args.no_cpu_baseline and world >= 1:
         steps_cpu = 6
-        ips, ms, cores = cpu_eval_images_per_s({k: v.cpu() for k, v in model.state_dict().items()}, 64, steps_cpu, 2)
+        ips, ms, cores = cpu_eval_images_per_s({k: v.cpu() for k, v in model.state_dict().items()}, 64, steps_cpu, 2,
+                                               arch=args.model)
         line["cpu_baseline"] = {"value": round(ips, 2), "unit": UNIT, "cores": cores, "kind": "port",
-                                "sample": f"{steps_cpu} timed steps x 64 images (+2 warm-up), oracle/effnet_b0.py fp32 eager, "
+                                "sample": f"{steps_cpu} timed steps x 64 images (+2 warm-up), oracle/{args.model.replace('efficientnet', 'effnet')}.py fp32 eager, "
                                           f"torch threads={cores}, os.cpu_count={os.cpu_count()}"}
     print(json.dumps(line), flush=True)
 

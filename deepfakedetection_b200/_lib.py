@@ -20,6 +20,7 @@ LIB_PATH = Path(os.environ["B200DF_LIB"]).resolve() if os.environ.get("B200DF_LI
 OK = 0
 E_INVALID, E_STATE, E_CUDA, E_NO_DEVICE, E_WORKSPACE = -1, -2, -3, -4, -5
 ARCH_EFFICIENTNET_B0 = 0
+ARCH_EFFICIENTNET_B3 = 1
 PREC_BF16, PREC_FP32 = 0, 1
 DT_BF16, DT_FP32 = 0, 1
 
@@ -35,6 +36,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200df_set_tensor": (_i, [_vp, C.c_char_p, _vp, _sz, _i]),
     "b200df_num_tensors": (_i, [_vp]),
     "b200df_tensor_info": (_i, [_vp, _i, C.POINTER(C.c_char_p), C.POINTER(_sz)]),
+    "b200df_feature_shape": (_i, [_vp, C.POINTER(_i), C.POINTER(_i)]),
     "b200df_finalize": (_i, [_vp, _i]),
     "b200df_workspace_bytes": (_i, [_vp, _i, _i, C.POINTER(_sz)]),
     "b200df_forward": (_i, [_vp, _vp, _i, _vp, _vp, _sz, _vp]),

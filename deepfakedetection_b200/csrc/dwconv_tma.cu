@@ -70,7 +70,9 @@ __device__ __forceinline__ f32x2 bf16x2_to_f32x2(uint32_t raw) {
 struct DwTile { int cb, tx, ty, ng; };
 
 // (Three CTAs per SM for the 3x3 single-column variants -- 80 registers, <= 74 KB plans -- measured slower.)
-template <int K, int S, int TH, int NC>
+// PL: zero rows/columns before the image.  (K-1)/2 everywhere except the TF-"same" 3x3 stride-2 layers of the
+// efficientnet_pytorch layout (pad (0, 1): PL = 0, the box then starts on the even column 2*ox itself).
+template <int K, int S, int TH, int NC, int PL = (K - 1) / 2>
 __global__ void __launch_bounds__(256, 2)
 dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -82,8 +84,8 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
   float* spool = reinterpret_cast<float*>(smem + 2 * p.stage_stride);
   const int spool_stage = nwarps_ * p.gimg * kDwCB;
 
-  constexpr int PAD = (K - 1) / 2;
-  constexpr int PADE = (S == 2) ? 2 : PAD;   // stride 2: the box starts on an even column
+  constexpr int PAD = PL;
+  constexpr int PADE = (S == 2) ? (PL == 0 ? 0 : 2) : PAD;   // stride 2: the box starts on an even column
   constexpr int XOFF = PADE - PAD;           // extra left columns inside the box
   constexpr int RIN = (TH - 1) * S + K;      // input rows one strip touches
 
@@ -331,9 +333,9 @@ int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsign
 
 namespace {
 
-template <int K, int S, int TH, int NC>
+template <int K, int S, int TH, int NC, int PL = (K - 1) / 2>
 cudaError_t dw_tma_launch(const DwPlan& pl, cudaStream_t s) {
-  auto kern = dwconv_tma_kernel<K, S, TH, NC>;
+  auto kern = dwconv_tma_kernel<K, S, TH, NC, PL>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -344,16 +346,18 @@ cudaError_t dw_tma_launch(const DwPlan& pl, cudaStream_t s) {
   return launch_pdl(kern, dim3(pl.grid), dim3(pl.block), pl.smem, s, *reinterpret_cast<const CUtensorMap*>(pl.tmap), pl.p);
 }
 
-template <int K, int S, int TH, int NC>
+template <int K, int S, int TH, int NC, int PL = (K - 1) / 2>
 int dw_tma_occupancy(int block, size_t smem) {
-  auto kern = dwconv_tma_kernel<K, S, TH, NC>;
+  auto kern = dwconv_tma_kernel<K, S, TH, NC, PL>;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) return 1;
   int nb = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, block, smem) != cudaSuccess || nb < 1) nb = 1;
   return nb;
 }
 
-int dw_tma_occupancy_dispatch(int k, int stride, int th, int nc, int block, size_t smem) {
+int dw_tma_occupancy_dispatch(int k, int stride, int th, int nc, int pad_lo, int block, size_t smem) {
+  if (k == 3 && stride == 2 && nc == 1 && pad_lo == 0)
+    return th == 8 ? dw_tma_occupancy<3, 2, 8, 1, 0>(block, smem) : dw_tma_occupancy<3, 2, 7, 1, 0>(block, smem);
 #define DW_OCC(K_, S_, TH_, NC_) \
   if (k == K_ && stride == S_ && th == TH_ && nc == NC_) return dw_tma_occupancy<K_, S_, TH_, NC_>(block, smem)
   DW_OCC(3, 1, 8, 1); DW_OCC(3, 1, 7, 1); DW_OCC(3, 2, 8, 1); DW_OCC(3, 2, 7, 1);
@@ -377,7 +381,7 @@ static size_t dw_smem_limit() {  // B200DF_DW_SMEM_KB: sweep aid (e.g. 74 -> pla
 }  // namespace
 
 int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                    const float* bias, void* out, pool_t* pool) {
+                    const float* bias, void* out, pool_t* pool, int pad_lo) {
   plan.tc = 0;
   {  // EXPERIMENT, off by default (B200DF_DW_TC=1): stride-1 layers on the tensor cores (dwconv_tc.cu).
      // Measured 2x SLOWER than this CUDA-core kernel: every tap re-streams the whole pixel tile from shared
@@ -387,13 +391,16 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
       const char* e = getenv("B200DF_DW_TC");
       use_tc = (e && e[0] == '1') ? 1 : 0;
     }
-    if (use_tc && plan_dwconv_tc(plan, x, n, h, w, c, k, stride, wgt, bias, out, pool) == 0) return 0;
+    if (use_tc && pad_lo < 0 && plan_dwconv_tc(plan, x, n, h, w, c, k, stride, wgt, bias, out, pool) == 0) return 0;
     plan.tc = 0;
   }
   if (n <= 0 || c % 8 || (k != 3 && k != 5) || (stride != 1 && stride != 2)) return -1;
   if (stride == 2 && (w & 1)) return -1;
-  const int pad = (k - 1) / 2;
-  const int Ho = (h + 2 * pad - k) / stride + 1, Wo = (w + 2 * pad - k) / stride + 1;
+  const int pad = pad_lo < 0 ? (k - 1) / 2 : pad_lo;
+  // an explicit pad-before other than (k-1)/2 exists only for the TF-"same" 3x3 stride-2 layers: pad (0, 1)
+  if (pad != (k - 1) / 2 && !(pad == 0 && k == 3 && stride == 2 && !(h & 1))) return -1;
+  const int pade = stride == 2 ? (pad == 0 ? 0 : 2) : pad;  // the stride-2 box starts on an even column
+  const int Ho = (h - 1) / stride + 1, Wo = (w - 1) / stride + 1;  // total padding is k - 1 either way
   // choose the strip height TH and the output tile: even width wasting at most one column, height a multiple
   // of TH dividing the strip count; maximise useful/loaded pixels subject to the per-stage smem limit, prefer
   // >= 8 warp items.  A few EfficientNet-B0 shapes have measured-better plans (tools/dw_sweep.py on a B200);
@@ -441,7 +448,7 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
           bw = otw + k - 1;
           bytes = (size_t)bw * bh * 64;
         } else {
-          const int cols = (otw - 1) * 2 + k + (2 - pad);  // incl. the even-start offset
+          const int cols = (otw - 1) * 2 + k + (pade - pad);  // incl. the even-start offset
           bw = (cols + 1) / 2;                              // column pairs
           bytes = (size_t)bw * 2 * bh * 64;
         }
@@ -493,12 +500,12 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
     rc = encode_tmap_nd_bf16(plan.tmap, x, 5, dims, str, box, 0);
   }
   if (rc) return rc;
-  plan.k = k; plan.stride = stride; plan.th = th; plan.nc = nc;
+  plan.k = k; plan.stride = stride; plan.th = th; plan.nc = nc; plan.pad_lo = pad;
   const int items = col_groups * b_m * b_g;
   plan.block = items >= 8 ? 256 : (items >= 4 ? 128 : 64);
   plan.smem = 1024 + 2 * (size_t)p.stage_stride + 2 * (size_t)(plan.block / 32) * b_g * kDwCB * sizeof(float);
   const long long total = (long long)p.tiles_x * p.tiles_y * p.ncb * ((n + b_g - 1) / b_g);
-  const int per_sm = dw_tma_occupancy_dispatch(k, stride, th, nc, plan.block, plan.smem);
+  const int per_sm = dw_tma_occupancy_dispatch(k, stride, th, nc, pad, plan.block, plan.smem);
   long long grid = std::min<long long>(total, (long long)kNumSMs * per_sm);
   p.cb_fixed = 0;
   if (grid >= p.ncb) {  // a grid that is a multiple of ncb keeps every CTA on one channel block
@@ -512,6 +519,8 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
 
 cudaError_t launch_dwconv_tma(const DwPlan& pl, cudaStream_t s) {
   if (pl.tc) return launch_dwconv_tc(pl, s);
+  if (pl.k == 3 && pl.stride == 2 && pl.nc == 1 && pl.pad_lo == 0)
+    return pl.th == 8 ? dw_tma_launch<3, 2, 8, 1, 0>(pl, s) : dw_tma_launch<3, 2, 7, 1, 0>(pl, s);
 #define DW_CASE(K_, S_, TH_, NC_) \
   if (pl.k == K_ && pl.stride == S_ && pl.th == TH_ && pl.nc == NC_) return dw_tma_launch<K_, S_, TH_, NC_>(pl, s)
   DW_CASE(3, 1, 8, 1); DW_CASE(3, 1, 7, 1); DW_CASE(3, 2, 8, 1); DW_CASE(3, 2, 7, 1);

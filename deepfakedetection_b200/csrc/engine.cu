@@ -90,65 +90,114 @@ static void add_bn(b200df_engine* e, const std::string& p, int c) {
   add_slot(e, p + ".running_var", c);
 }
 
-static void describe_effnet_b0(b200df_engine* e) {
-  struct Stage { bool ds; int k, s, exp, cout, reps; };
-  static const Stage stages[7] = {{true, 3, 1, 1, 16, 1},  {false, 3, 2, 6, 24, 2},  {false, 5, 2, 6, 40, 2},
-                                  {false, 3, 2, 6, 80, 3}, {false, 5, 1, 6, 112, 3}, {false, 5, 2, 6, 192, 4},
-                                  {false, 3, 1, 6, 320, 1}};
-  add_slot(e, "conv_stem.weight", 32 * 27);
-  add_bn(e, "bn1", 32);
-  int cin = 32, h = e->img / 2;
-  for (int s = 0; s < 7; ++s) {
-    for (int r = 0; r < stages[s].reps; ++r) {
+struct StageCfg { int k, s, exp, cout, reps; };
+
+// Shared by both layouts: walks the stage table, registers every tensor under the layout's names.
+// timm_layout: blocks.S.R.{conv_pw,bn1,conv_dw,bn2,se.conv_reduce,se.conv_expand,conv_pwl,bn3} (the expand-less
+// first stage is a DepthwiseSeparableConv: conv_dw,bn1,se,conv_pw,bn2).  Otherwise efficientnet_pytorch:
+// _blocks.N.{_expand_conv,_bn0,_depthwise_conv,_bn1,_se_reduce,_se_expand,_project_conv,_bn2}, flat block index.
+static void describe_blocks(b200df_engine* e, const StageCfg* stages, int nstages, bool timm_layout, bool tf_same) {
+  int cin = e->stem_c, h = e->img / 2, flat = 0;
+  for (int s = 0; s < nstages; ++s) {
+    for (int r = 0; r < stages[s].reps; ++r, ++flat) {
       BlockCfg b;
-      b.prefix = "blocks." + std::to_string(s) + "." + std::to_string(r) + ".";
-      b.expand = !stages[s].ds;
+      b.expand = stages[s].exp != 1;
       b.cin = cin;
       b.cout = stages[s].cout;
-      b.mid = b.expand ? cin * stages[s].exp : cin;
+      b.mid = cin * stages[s].exp;
       b.k = stages[s].k;
       b.stride = r == 0 ? stages[s].s : 1;
       b.skip = (b.stride == 1 && b.cin == b.cout);
-      b.rd = cin / 4 > 0 ? cin / 4 : 1;
+      b.rd = cin / 4 > 0 ? cin / 4 : 1;  // timm: make_divisible off for se (rd = cin/4); e_p: max(1, int(cin*0.25))
       b.hin = h;
-      b.hout = (h + 2 * ((b.k - 1) / 2) - b.k) / b.stride + 1;
-      const std::string& p = b.prefix;
-      if (b.expand) {
-        add_slot(e, p + "conv_pw.weight", (size_t)b.mid * b.cin);
-        add_bn(e, p + "bn1", b.mid);
-        add_slot(e, p + "conv_dw.weight", (size_t)b.mid * b.k * b.k);
-        add_bn(e, p + "bn2", b.mid);
+      b.hout = (h - 1) / b.stride + 1;   // total padding k-1 in both layouts
+      // Conv2dStaticSamePadding at the 300-pixel native size: only the 3x3 stride-2 layers are asymmetric, (0, 1)
+      b.pad_lo = (tf_same && b.k == 3 && b.stride == 2) ? 0 : -1;
+      if (timm_layout) {
+        const std::string p = "blocks." + std::to_string(s) + "." + std::to_string(r) + ".";
+        b.prefix = p;
+        if (b.expand) {
+          b.n_expand_w = p + "conv_pw.weight"; b.n_expand_bn = p + "bn1";
+          b.n_dw_w = p + "conv_dw.weight";     b.n_dw_bn = p + "bn2";
+          b.n_proj_w = p + "conv_pwl.weight";  b.n_proj_bn = p + "bn3";
+        } else {
+          b.n_dw_w = p + "conv_dw.weight";     b.n_dw_bn = p + "bn1";
+          b.n_proj_w = p + "conv_pw.weight";   b.n_proj_bn = p + "bn2";
+        }
+        b.n_se_rw = p + "se.conv_reduce.weight"; b.n_se_rb = p + "se.conv_reduce.bias";
+        b.n_se_ew = p + "se.conv_expand.weight"; b.n_se_eb = p + "se.conv_expand.bias";
       } else {
-        add_slot(e, p + "conv_dw.weight", (size_t)b.mid * b.k * b.k);
-        add_bn(e, p + "bn1", b.mid);
+        const std::string p = "_blocks." + std::to_string(flat) + ".";
+        b.prefix = p;
+        if (b.expand) { b.n_expand_w = p + "_expand_conv.weight"; b.n_expand_bn = p + "_bn0"; }
+        b.n_dw_w = p + "_depthwise_conv.weight"; b.n_dw_bn = p + "_bn1";
+        b.n_se_rw = p + "_se_reduce.weight";     b.n_se_rb = p + "_se_reduce.bias";
+        b.n_se_ew = p + "_se_expand.weight";     b.n_se_eb = p + "_se_expand.bias";
+        b.n_proj_w = p + "_project_conv.weight"; b.n_proj_bn = p + "_bn2";
       }
-      add_slot(e, p + "se.conv_reduce.weight", (size_t)b.rd * b.mid);
-      add_slot(e, p + "se.conv_reduce.bias", b.rd);
-      add_slot(e, p + "se.conv_expand.weight", (size_t)b.mid * b.rd);
-      add_slot(e, p + "se.conv_expand.bias", b.mid);
+      // registration order = state_dict order of the layout
       if (b.expand) {
-        add_slot(e, p + "conv_pwl.weight", (size_t)b.cout * b.mid);
-        add_bn(e, p + "bn3", b.cout);
-      } else {
-        add_slot(e, p + "conv_pw.weight", (size_t)b.cout * b.mid);
-        add_bn(e, p + "bn2", b.cout);
+        add_slot(e, b.n_expand_w, (size_t)b.mid * b.cin);
+        add_bn(e, b.n_expand_bn, b.mid);
       }
+      add_slot(e, b.n_dw_w, (size_t)b.mid * b.k * b.k);
+      add_bn(e, b.n_dw_bn, b.mid);
+      add_slot(e, b.n_se_rw, (size_t)b.rd * b.mid);
+      add_slot(e, b.n_se_rb, b.rd);
+      add_slot(e, b.n_se_ew, (size_t)b.mid * b.rd);
+      add_slot(e, b.n_se_eb, b.mid);
+      add_slot(e, b.n_proj_w, (size_t)b.cout * b.mid);
+      add_bn(e, b.n_proj_bn, b.cout);
       e->blocks.push_back(b);
       cin = b.cout;
       h = b.hout;
     }
   }
-  add_slot(e, "conv_head.weight", (size_t)1280 * cin);
-  add_bn(e, "bn2", 1280);
-  add_slot(e, "classifier.weight", (size_t)e->num_classes * 1280);
-  add_slot(e, "classifier.bias", e->num_classes);
+}
+
+static void describe_tail(b200df_engine* e) {
+  add_slot(e, e->n_head_w, (size_t)e->head_c * e->blocks.back().cout);
+  add_bn(e, e->n_head_bn, e->head_c);
+  add_slot(e, e->n_fc_w, (size_t)e->num_classes * e->head_c);
+  add_slot(e, e->n_fc_b, e->num_classes);
+}
+
+static void describe_effnet_b0(b200df_engine* e) {
+  static const StageCfg stages[7] = {{3, 1, 1, 16, 1},  {3, 2, 6, 24, 2},  {5, 2, 6, 40, 2}, {3, 2, 6, 80, 3},
+                                     {5, 1, 6, 112, 3}, {5, 2, 6, 192, 4}, {3, 1, 6, 320, 1}};
+  e->stem_c = 32; e->head_c = 1280; e->stem_pad = 1; e->bn_eps = 1e-5f;
+  e->n_stem_w = "conv_stem.weight"; e->n_stem_bn = "bn1";
+  e->n_head_w = "conv_head.weight"; e->n_head_bn = "bn2";
+  e->n_fc_w = "classifier.weight";  e->n_fc_b = "classifier.bias";
+  add_slot(e, e->n_stem_w, (size_t)e->stem_c * 27);
+  add_bn(e, e->n_stem_bn, e->stem_c);
+  describe_blocks(e, stages, 7, true, false);
+  describe_tail(e);
+}
+
+// EfficientNet-B3 as built by efficientnet_pytorch `EfficientNet.from_name("efficientnet-b3")`
+// (/root/reference/orchestration/model_registry.py:32-36, 50-58): width x1.2 / depth x1.4 of
+// the base table (stem 40, stages 24/32/48/96/136/232/384 x 2/3/3/5/5/6/2, head 1536), BN eps 1e-3, SE squeeze
+// int(cin/4), static TF-"same" padding computed for 300 pixels and applied to the 224-pixel crops.
+static void describe_effnet_b3(b200df_engine* e) {
+  static const StageCfg stages[7] = {{3, 1, 1, 24, 2},  {3, 2, 6, 32, 3},  {5, 2, 6, 48, 3}, {3, 2, 6, 96, 5},
+                                     {5, 1, 6, 136, 5}, {5, 2, 6, 232, 6}, {3, 1, 6, 384, 2}};
+  e->stem_c = 40; e->head_c = 1536; e->stem_pad = 0; e->bn_eps = 1e-3f;
+  e->n_stem_w = "_conv_stem.weight"; e->n_stem_bn = "_bn0";
+  e->n_head_w = "_conv_head.weight"; e->n_head_bn = "_bn1";
+  e->n_fc_w = "_fc.weight";          e->n_fc_b = "_fc.bias";
+  add_slot(e, e->n_stem_w, (size_t)e->stem_c * 27);
+  add_bn(e, e->n_stem_bn, e->stem_c);
+  describe_blocks(e, stages, 7, false, true);
+  describe_tail(e);
 }
 
 // ---- lifecycle ----------------------------------------------------------------------------------------
 extern "C" int b200df_create(int arch, int num_classes, int device, b200df_handle* out) {
   if (!out) return fail(B200DF_E_INVALID, "out is NULL");
   *out = nullptr;
-  if (arch != B200DF_ARCH_EFFICIENTNET_B0) return fail(B200DF_E_INVALID, "unknown arch id %d", arch);
+  if (arch != B200DF_ARCH_EFFICIENTNET_B0 && arch != B200DF_ARCH_EFFICIENTNET_B3)
+    return fail(B200DF_E_INVALID, "unknown arch id %d", arch);
   if (num_classes < 1 || num_classes > 4096) return fail(B200DF_E_INVALID, "num_classes %d out of range", num_classes);
   // No device is needed to describe a model (tests list the expected tensors on CPU boxes);
   // finalize() and every compute entry point require an sm_100 device and never fall back.
@@ -156,7 +205,8 @@ extern "C" int b200df_create(int arch, int num_classes, int device, b200df_handl
   e->arch = arch;
   e->num_classes = num_classes;
   e->device = device;
-  describe_effnet_b0(e);
+  if (arch == B200DF_ARCH_EFFICIENTNET_B3) describe_effnet_b3(e);
+  else describe_effnet_b0(e);
   *out = e;
   return B200DF_OK;
 }
@@ -192,6 +242,13 @@ extern "C" int b200df_tensor_info(b200df_handle h, int index, const char** name,
   if (!h || index < 0 || index >= (int)h->slots.size()) return fail(B200DF_E_INVALID, "tensor index out of range");
   if (name) *name = h->slots[index].name.c_str();
   if (numel) *numel = h->slots[index].numel;
+  return B200DF_OK;
+}
+
+extern "C" int b200df_feature_shape(b200df_handle h, int* channels, int* side) {
+  if (!h || h->blocks.empty()) return fail(B200DF_E_INVALID, "NULL handle");
+  if (channels) *channels = h->head_c;
+  if (side) *side = h->blocks.back().hout;
   return B200DF_OK;
 }
 
@@ -245,7 +302,7 @@ void bn_fold(const b200df_engine* e, const std::string& p, int c, std::vector<fl
   scale.resize(c);
   shift.resize(c);
   for (int i = 0; i < c; ++i) {
-    float s = g[i] / sqrtf(v[i] + 1e-5f);
+    float s = g[i] / sqrtf(v[i] + e->bn_eps);
     scale[i] = s;
     shift[i] = b[i] - m[i] * s;
   }
@@ -316,9 +373,9 @@ extern "C" int b200df_finalize(b200df_handle h, int precision) {
   Packer pk;
   std::vector<float> sc, sh, tmp;
   // stem
-  bn_fold(h, "bn1", 32, sc, sh);
-  tmp = T(h, "conv_stem.weight");
-  for (int oc = 0; oc < 32; ++oc)
+  bn_fold(h, h->n_stem_bn, h->stem_c, sc, sh);
+  tmp = T(h, h->n_stem_w);
+  for (int oc = 0; oc < h->stem_c; ++oc)
     for (int t = 0; t < 27; ++t) tmp[oc * 27 + t] *= sc[oc];
   const size_t stem_w = pack_f32(pk, tmp), stem_b = pack_f32(pk, sh);
 
@@ -329,15 +386,14 @@ extern "C" int b200df_finalize(b200df_handle h, int precision) {
   for (size_t i = 0; i < h->blocks.size(); ++i) {
     const BlockCfg& b = h->blocks[i];
     BlockDev& d = h->bdev[i];
-    const std::string& p = b.prefix;
     if (b.expand) {
-      bn_fold(h, p + "bn1", b.mid, sc, sh);
-      boff[i].ex = pack_pw(pk, d.expand, T(h, p + "conv_pw.weight"), b.mid, b.cin, sc, sh, precision);
+      bn_fold(h, b.n_expand_bn, b.mid, sc, sh);
+      boff[i].ex = pack_pw(pk, d.expand, T(h, b.n_expand_w), b.mid, b.cin, sc, sh, precision);
     }
     // depthwise: [mid,1,k,k] -> tap-major [k*k, mid], BN folded
-    bn_fold(h, p + (b.expand ? "bn2" : "bn1"), b.mid, sc, sh);
+    bn_fold(h, b.n_dw_bn, b.mid, sc, sh);
     {
-      const auto& w = T(h, p + "conv_dw.weight");
+      const auto& w = T(h, b.n_dw_w);
       const int kk = b.k * b.k;
       tmp.assign((size_t)kk * b.mid, 0.f);
       for (int c = 0; c < b.mid; ++c)
@@ -346,30 +402,29 @@ extern "C" int b200df_finalize(b200df_handle h, int precision) {
       boff[i].dw_b = pack_f32(pk, sh);
     }
     // squeeze-excite
-    boff[i].w1 = pack_f32(pk, T(h, p + "se.conv_reduce.weight"));
-    boff[i].b1 = pack_f32(pk, T(h, p + "se.conv_reduce.bias"));
+    boff[i].w1 = pack_f32(pk, T(h, b.n_se_rw));
+    boff[i].b1 = pack_f32(pk, T(h, b.n_se_rb));
     {
-      const auto& w2 = T(h, p + "se.conv_expand.weight");  // [mid, rd]
+      const auto& w2 = T(h, b.n_se_ew);  // [mid, rd]
       tmp.assign((size_t)b.rd * b.mid, 0.f);
       for (int c = 0; c < b.mid; ++c)
         for (int j = 0; j < b.rd; ++j) tmp[(size_t)j * b.mid + c] = w2[(size_t)c * b.rd + j];
       boff[i].w2t = pack_f32(pk, tmp);
     }
-    boff[i].b2 = pack_f32(pk, T(h, p + "se.conv_expand.bias"));
+    boff[i].b2 = pack_f32(pk, T(h, b.n_se_eb));
     // project
-    bn_fold(h, p + (b.expand ? "bn3" : "bn2"), b.cout, sc, sh);
-    boff[i].pr = pack_pw(pk, d.project, T(h, p + (b.expand ? "conv_pwl.weight" : "conv_pw.weight")), b.cout, b.mid,
-                         sc, sh, precision);
+    bn_fold(h, b.n_proj_bn, b.cout, sc, sh);
+    boff[i].pr = pack_pw(pk, d.project, T(h, b.n_proj_w), b.cout, b.mid, sc, sh, precision);
     d.pool_off = pool_off;
     pool_off += (size_t)b.mid;
   }
   h->pool_floats_per_img = pool_off;
   // head: conv_head stays un-folded (its raw output is the Grad-CAM activation); bn2 -> scale/shift
   const int cin_head = h->blocks.back().cout;
-  PwOff head_off = pack_pw(pk, h->head, T(h, "conv_head.weight"), 1280, cin_head, {}, {}, precision);
-  bn_fold(h, "bn2", 1280, sc, sh);
+  PwOff head_off = pack_pw(pk, h->head, T(h, h->n_head_w), h->head_c, cin_head, {}, {}, precision);
+  bn_fold(h, h->n_head_bn, h->head_c, sc, sh);
   const size_t hs = pack_f32(pk, sc), hb = pack_f32(pk, sh);
-  const size_t fw = pack_f32(pk, T(h, "classifier.weight")), fb = pack_f32(pk, T(h, "classifier.bias"));
+  const size_t fw = pack_f32(pk, T(h, h->n_fc_w)), fb = pack_f32(pk, T(h, h->n_fc_b));
 
   h->arena_bytes = (pk.buf.size() + 1023) & ~size_t(1023);
   CU_OK(cudaMalloc(&h->arena, h->arena_bytes));
@@ -414,7 +469,7 @@ extern "C" int b200df_finalize(b200df_handle h, int precision) {
 // ---- workspace ------------------------------------------------------------------------------------------
 static Workspace layout_workspace(const b200df_engine* h, int n) {
   const size_t es = h->precision == B200DF_PREC_BF16 ? 2 : 4;
-  size_t trunk = (size_t)32 * (h->img / 2) * (h->img / 2);  // stem output
+  size_t trunk = (size_t)h->stem_c * (h->img / 2) * (h->img / 2);  // stem output
   size_t e = 0, d = 0;
   for (const auto& b : h->blocks) {
     trunk = std::max(trunk, (size_t)b.cout * b.hout * b.hout);
@@ -429,10 +484,10 @@ static Workspace layout_workspace(const b200df_engine* h, int n) {
   w.t1 = off; off += al(trunk * n * es);
   w.e = off; off += al(e * n * es);
   w.d = off; off += al(d * n * es);
-  w.a = off; off += al((size_t)1280 * hw * n * es);
+  w.a = off; off += al((size_t)h->head_c * hw * n * es);
   w.pool = off; off += al(h->pool_floats_per_img * n * sizeof(pool_t));
   w.gate = off; off += al(h->pool_floats_per_img * n * sizeof(float));
-  w.pooled = off; off += al((size_t)1280 * n * sizeof(float));
+  w.pooled = off; off += al((size_t)h->head_c * n * sizeof(float));
   w.logits = off; off += al((size_t)h->num_classes * n * sizeof(float));
   w.cam_low = off; off += al((size_t)hw * n * sizeof(float));
   w.total = off;
@@ -534,13 +589,14 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
   const double es = h->precision == B200DF_PREC_BF16 ? 2.0 : 4.0;
   const double ho0 = h->img / 2;
   ProfRec* pr = prof_begin(h, s, "stem", -1,
-                           (double)n * (3.0 * h->img * h->img * (in_kind == kInF32NCHW ? 4.0 : 1.0) + ho0 * ho0 * 32 * es),
-                           2.0 * n * ho0 * ho0 * 32 * 27);
+                           (double)n * (3.0 * h->img * h->img * (in_kind == kInF32NCHW ? 4.0 : 1.0) + ho0 * ho0 * h->stem_c * es),
+                           2.0 * n * ho0 * ho0 * h->stem_c * 27);
   if (in_kind == kInF32NCHW) {
-    CU_OK(launch_stem(reinterpret_cast<const float*>(images), n, h->img, h->img, h->stem_w, h->stem_b, cur, dt, s));
+    CU_OK(launch_stem(reinterpret_cast<const float*>(images), n, h->img, h->img, h->stem_w, h->stem_b, cur, dt, s,
+                      h->stem_c, h->stem_pad));
   } else {
     CU_OK(launch_stem_u8(reinterpret_cast<const uint8_t*>(images), n, h->img, h->img, h->stem_w, h->stem_b, in_sc[0],
-                         in_sc[1], in_sc[2], in_sh[0], in_sh[1], in_sh[2], cur, dt, s));
+                         in_sc[1], in_sc[2], in_sh[0], in_sh[1], in_sh[2], cur, dt, s, h->stem_c, h->stem_pad));
   }
   prof_end(pr, s);
   int gi = 0;
@@ -569,7 +625,8 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
         DwPlan& dp = h->plan.dws[i];
         if (dp.x != dw_in || dp.p.n != n || dp.p.pool != pool_b) {
           dp.x = nullptr;
-          if (plan_dwconv_tma(dp, dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b) != 0)
+          if (plan_dwconv_tma(dp, dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b,
+                              b.pad_lo) != 0)
             dp.x = nullptr;
         }
         if (dp.x != nullptr) {
@@ -578,7 +635,8 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
         }
       }
       if (!done)
-        CU_OK(launch_dwconv(dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b, dt, s));
+        CU_OK(launch_dwconv(dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b, dt, s,
+                            b.pad_lo));
     }
     prof_end(pr, s);
     pr = prof_begin(h, s, "se", li, (double)n * b.mid * 8.0 + 2.0 * b.mid * b.rd * 4.0, 4.0 * n * b.mid * b.rd);
@@ -596,8 +654,8 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
   }
   const int hw = h->blocks.back().hout * h->blocks.back().hout;
   const int cin_head = h->blocks.back().cout;
-  pr = prof_begin(h, s, "conv_head", -1, (double)n * hw * (cin_head + 1280) * es + 1280.0 * cin_head * es,
-                  2.0 * n * hw * cin_head * 1280);
+  pr = prof_begin(h, s, "conv_head", -1, (double)n * hw * (cin_head + h->head_c) * es + (double)h->head_c * cin_head * es,
+                  2.0 * n * hw * cin_head * h->head_c);
   GemmCall g{&h->head, cur, (long long)n * hw, nullptr, 1, nullptr, 0, ws + W.a};
   int rc = run_gemm(h, g, gi++, s);
   prof_end(pr, s);
@@ -623,12 +681,12 @@ int run_head(b200df_engine* h, int n, uint8_t* ws, const Workspace& W, float* lo
   const int hw = h->blocks.back().hout * h->blocks.back().hout;
   float* pooled = reinterpret_cast<float*>(ws + W.pooled);
   const double es = h->precision == B200DF_PREC_BF16 ? 2.0 : 4.0;
-  ProfRec* pr = prof_begin(h, s, "head_pool", -1, (double)n * hw * 1280 * es + (double)n * 1280 * 4, 8.0 * n * hw * 1280);
-  CU_OK(launch_head_pool(ws + W.a, n, hw, 1280, h->head_scale, h->head_shift, pooled, dt, s));
+  ProfRec* pr = prof_begin(h, s, "head_pool", -1, (double)n * hw * h->head_c * es + (double)n * h->head_c * 4, 8.0 * n * hw * h->head_c);
+  CU_OK(launch_head_pool(ws + W.a, n, hw, h->head_c, h->head_scale, h->head_shift, pooled, dt, s));
   prof_end(pr, s);
-  pr = prof_begin(h, s, "classifier", -1, (double)n * 1280 * 4 + (double)n * h->num_classes * 4,
-                  2.0 * n * 1280 * h->num_classes);
-  CU_OK(launch_classifier(pooled, n, 1280, h->fc_w, h->fc_b, h->num_classes, logits, s));
+  pr = prof_begin(h, s, "classifier", -1, (double)n * h->head_c * 4 + (double)n * h->num_classes * 4,
+                  2.0 * n * h->head_c * h->num_classes);
+  CU_OK(launch_classifier(pooled, n, h->head_c, h->fc_w, h->fc_b, h->num_classes, logits, s));
   prof_end(pr, s);
   return B200DF_OK;
 }
@@ -686,8 +744,8 @@ extern "C" int b200df_forward_cam(b200df_handle h, const float* images, int n, c
   if (rc) return rc;
   float* low = cam_lowres ? cam_lowres : reinterpret_cast<float*>(ws + W.cam_low);
   const double es = dt == kBF16 ? 2.0 : 4.0;
-  ProfRec* pr = prof_begin(h, s, "cam", -1, (double)n * hw * 1280 * es + (double)n * hw * 4, 12.0 * n * hw * 1280);
-  CU_OK(launch_cam(ws + W.a, n, hw, 1280, h->head_scale, h->head_shift, h->fc_w, h->num_classes, target_cls, lg, low,
+  ProfRec* pr = prof_begin(h, s, "cam", -1, (double)n * hw * h->head_c * es + (double)n * hw * 4, 12.0 * n * hw * h->head_c);
+  CU_OK(launch_cam(ws + W.a, n, hw, h->head_c, h->head_scale, h->head_shift, h->fc_w, h->num_classes, target_cls, lg, low,
                    dt, s));
   prof_end(pr, s);
   if (cam) {
@@ -710,7 +768,7 @@ extern "C" int b200df_trunk(b200df_handle h, const float* images, int n, float* 
   const int hw = h->blocks.back().hout * h->blocks.back().hout;
   rc = run_trunk(h, images, kInF32NCHW, nullptr, nullptr, n, ws, W, s);
   if (rc) return rc;
-  CU_OK(launch_nhwc_to_nchw_f32(ws + W.a, n, hw, 1280, a_nchw, dt, s));
+  CU_OK(launch_nhwc_to_nchw_f32(ws + W.a, n, hw, h->head_c, a_nchw, dt, s));
   return B200DF_OK;
 }
 
@@ -719,7 +777,7 @@ extern "C" int b200df_trunk(b200df_handle h, const float* images, int n, float* 
 static int head_scratch(b200df_engine* h, int n, float** out) {
   static thread_local float* buf = nullptr;
   static thread_local size_t cap = 0;
-  size_t need = (size_t)n * 1280 * sizeof(float);
+  size_t need = (size_t)n * h->head_c * sizeof(float);
   if (need > cap) {
     if (buf) cudaFree(buf);
     buf = nullptr;
@@ -741,8 +799,8 @@ extern "C" int b200df_head(b200df_handle h, const float* a_nchw, int n, float* l
   float* pooled = nullptr;
   int rc = head_scratch(h, n, &pooled);
   if (rc) return rc;
-  CU_OK(launch_head_from_nchw(a_nchw, n, hw, 1280, h->head_scale, h->head_shift, pooled, s));
-  CU_OK(launch_classifier(pooled, n, 1280, h->fc_w, h->fc_b, h->num_classes, logits, s));
+  CU_OK(launch_head_from_nchw(a_nchw, n, hw, h->head_c, h->head_scale, h->head_shift, pooled, s));
+  CU_OK(launch_classifier(pooled, n, h->head_c, h->fc_w, h->fc_b, h->num_classes, logits, s));
   return B200DF_OK;
 }
 
@@ -753,7 +811,7 @@ extern "C" int b200df_head_backward(b200df_handle h, const float* a_nchw, const 
   if (!a_nchw || !grad_logits || !grad_a_nchw) return fail(B200DF_E_INVALID, "NULL argument");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int hw = h->blocks.back().hout * h->blocks.back().hout;
-  CU_OK(launch_head_backward(a_nchw, grad_logits, n, hw, 1280, h->head_scale, h->head_shift, h->fc_w, h->num_classes,
+  CU_OK(launch_head_backward(a_nchw, grad_logits, n, hw, h->head_c, h->head_scale, h->head_shift, h->fc_w, h->num_classes,
                              grad_a_nchw, s));
   return B200DF_OK;
 }

@@ -26,6 +26,9 @@ struct BlockCfg {
   bool skip = false;
   int cin = 0, mid = 0, cout = 0, k = 3, stride = 1, rd = 0;
   int hin = 0, hout = 0;  // square spatial sizes
+  int pad_lo = -1;        // depthwise zero rows/columns before the image; -1 = symmetric (k-1)/2
+  // state_dict names of this block's tensors ("" = absent); BN names are prefixes (.weight/.bias/.running_*)
+  std::string n_expand_w, n_expand_bn, n_dw_w, n_dw_bn, n_se_rw, n_se_rb, n_se_ew, n_se_eb, n_proj_w, n_proj_bn;
 };
 
 // A packed pointwise-conv (GEMM) layer on the device.
@@ -71,6 +74,10 @@ struct b200df_engine {
   int arch = 0, num_classes = 2, device = 0;
   int precision = -1;  // -1 = not finalized
   int img = 224;
+  // architecture constants (set by describe_*): stem/head widths, BN eps, stem pad-before, tensor names
+  int stem_c = 32, head_c = 1280, stem_pad = 1;
+  float bn_eps = 1e-5f;
+  std::string n_stem_w, n_stem_bn, n_head_w, n_head_bn, n_fc_w, n_fc_b;
   std::vector<b200df::TensorSlot> slots;
   std::map<std::string, int> slot_index;
   std::vector<b200df::BlockCfg> blocks;

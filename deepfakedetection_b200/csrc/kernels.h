@@ -34,13 +34,14 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 }
 
 // error plumbing: launchers return cudaError_t of the launch (cudaGetLastError()).
+// oc: stem channels (32 | 40).  pad: zero rows/columns BEFORE the image (1 symmetric, 0 = TF-"same" (0, 1)).
 cudaError_t launch_stem(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias,
-                        void* out, int dtype, cudaStream_t s);
+                        void* out, int dtype, cudaStream_t s, int oc = 32, int pad = 1);
 
 // u8 HWC input, fused ToTensor(/255)+Normalize: in_scale[c] = 1/(255*std[c]), in_shift[c] = -mean[c]/std[c]
 cudaError_t launch_stem_u8(const uint8_t* x_hwc, int n, int h, int w, const float* wgt, const float* bias,
                            float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, void* out,
-                           int dtype, cudaStream_t s);
+                           int dtype, cudaStream_t s, int oc = 32, int pad = 1);
 
 // Pooled sums are Q24 fixed-point int64 (common.cuh: pool_t), accumulated with integer atomics.
 typedef long long pool_t;
@@ -51,8 +52,10 @@ cudaError_t launch_stem_tc_u8(const uint8_t* x_hwc, int n, int h, int w, const f
                               float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, void* out,
                               cudaStream_t s);
 
+// pad_lo: zero rows/columns BEFORE the image; -1 = symmetric (k-1)/2.  The pad after is k - 1 - pad_lo, so the
+// output size (h - 1) / stride + 1 does not depend on it (efficientnet_pytorch Conv2dStaticSamePadding).
 cudaError_t launch_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                          const float* bias, void* out, pool_t* pool, int dtype, cudaStream_t s);
+                          const float* bias, void* out, pool_t* pool, int dtype, cudaStream_t s, int pad_lo = -1);
 
 struct DwTmaParams {
   int C, Ho, Wo;
@@ -91,6 +94,7 @@ struct DwPlan {
   DwTcParams q;
   int tc = 0;            // 1: planned for the tensor-core kernel
   int k = 0, stride = 0, th = 0;
+  int pad_lo = 1;        // zero rows/columns before the image: (k-1)/2, or 0 for the TF-"same" 3x3 stride-2 layers
   int nc = 1;            // output columns per thread (2: big stride-1 layers, columns x and x+2 share loaded inputs)
   int grid = 0, block = 0;
   size_t smem = 0;
@@ -98,7 +102,7 @@ struct DwPlan {
 };
 // bf16 only.  Returns 0 on success (plan filled), <0 if this shape is not supported by the TMA kernel.
 int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                    const float* bias, void* out, pool_t* pool);
+                    const float* bias, void* out, pool_t* pool, int pad_lo = -1);
 cudaError_t launch_dwconv_tma(const DwPlan& plan, cudaStream_t s);
 // Tensor-core variant (stride 1); plan_dwconv_tma tries it first, launch_dwconv_tma dispatches on plan.tc.
 int plan_dwconv_tc(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,

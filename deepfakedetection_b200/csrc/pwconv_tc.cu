@@ -42,7 +42,7 @@ constexpr int kScalWarps = 8;             // gated kernels: SE-gate scaler warps
 constexpr int kEpiWarps = 8;              // gated kernels: two groups of four (one group per TMEM accumulator)
 constexpr int kEpiWarpsWide = 16;         // ungated kernels (expand, conv_head: wide N, SiLU): two column halves per group
 constexpr int kEpiStageBytes = 32 * 128;  // one staging tile: 32 rows x 64 bf16; TWO per epilogue warp
-constexpr int kMaxBiasFloats = 1536;
+constexpr int kMaxBiasFloats = 2304;  // widest layer: EfficientNet-B3 expand 384 -> 2304
 
 struct TcParams {
   int m, cin, cout, cout_pad, bn;
@@ -192,6 +192,12 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     tmem_relinquish();
   }
   for (int i = threadIdx.x; i < p.cout_pad; i += blockDim.x) sbias[i] = __ldg(p.bias + i);
+  // K tails that are not a multiple of 16 (cin = 40, 24: the first EfficientNet-B3 blocks): the last MMA step reads
+  // 8 columns past cin, where the operand tiles are TMA-zero-filled but the gate slice holds whatever shared memory
+  // held (the bulk copy writes only cin - c_k floats) -- 0 x NaN garbage = NaN.  Start from zeros: entries that go
+  // stale later are finite gates.
+  if constexpr (kGate)
+    for (int i = threadIdx.x; i < kMaxStages * kBK; i += blockDim.x) sgate[i] = 0.f;
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -436,14 +442,18 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     PROF_WAIT(1, if (p.b_res) mbar_wait(bres_bar, 0))
     // (n tile, M sub-tile, image) of the current tile, advanced by the grid stride in mixed radix (no divisions)
     TileIter ti(t_begin, t_step, p.n_tiles, p.tiles_per_img);
-    const int kq_max = p.cin >> 3;
     int s = sgrp;                   // ring slot of this group's next chunk (kScalGroups <= stages)
     uint32_t ph = 0;
     int kc = sgrp, t = t_begin;
     while (kc >= p.k_chunks) { kc -= p.k_chunks; t += t_step; ti.next(); }
     while (t < t_end) {
       const int nrows = p.scale_b ? p.bn : min(kBM, p.rpi - ti.sub * kBM);  // rows of the tile to scale
-      const bool k_ok = kc * (kBK / 8) + lc < kq_max;
+      // every 16-B chunk the MMA will read: K tails are issued in steps of 16 columns, so for cin % 16 == 8 the
+      // last step reads one chunk past cin.  That chunk is zero in the source (TMA fill) and must be WRITTEN when
+      // the scaled copy goes to a ring slot no TMA load ever touched (b_res); its gate entries are the zeros the
+      // prologue put there.
+      const int krem = p.cin - kc * kBK;
+      const bool k_ok = lc < (krem >= kBK ? 8 : 2 * ((krem + 15) >> 4));
       PROF_WAIT(0, mbar_wait(&full_bar[s], ph))
       PROF_BEGIN
       if (k_ok) {

@@ -16,15 +16,17 @@
 
 namespace b200df {
 
-constexpr int kStemOC = 32;
 constexpr int kStemTR = 4;  // output rows per block
 constexpr int kStemThreads = 256;
 
-template <typename TOut, bool kU8>
+// kStemOC: 32 (timm B0) or 40 (efficientnet_pytorch B3).  pad: rows/columns of zero padding BEFORE the image
+// (1 = symmetric; 0 = the TF-"same" static padding (0, 1) efficientnet_pytorch computes for its 300-pixel
+// native size, /root/reference/orchestration/model_registry.py:32-36 -> Conv2dStaticSamePadding).
+template <typename TOut, bool kU8, int kStemOC>
 __global__ void __launch_bounds__(kStemThreads)
 stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict__ wgt,
             const float* __restrict__ bias, TOut* __restrict__ out, float sc0, float sc1, float sc2,
-            float sh0, float sh1, float sh2) {
+            float sh0, float sh1, float sh2, int pad) {
   extern __shared__ float smem[];
   const int Ho = H >> 1, Wo = W >> 1;
   const int PW = W + 2;                  // patch width incl. left/right halo column
@@ -35,7 +37,8 @@ stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict_
 
   const int n = blockIdx.y;
   const int oh0 = blockIdx.x * kStemTR;
-  const int ih0 = 2 * oh0 - 1;
+  const int ih0 = 2 * oh0 - pad;
+  const int xoff = 1 - pad;  // patch column 0 is input column -1
   const int tid = threadIdx.x;
 
   for (int i = tid; i < 27 * kStemOC; i += kStemThreads) {
@@ -102,11 +105,11 @@ stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict_
     for (int c = 0; c < 3; ++c) {
 #pragma unroll
       for (int ky = 0; ky < 3; ++ky) {
-        const float* prow = patch + (c * PR + 2 * r + ky) * PW + 2 * ow0;
+        const float* prow = patch + (c * PR + 2 * r + ky) * PW + 2 * ow0 + xoff;
         unsigned long long v[5];
 #pragma unroll
         for (int i = 0; i < 5; ++i) {
-          const float t = (2 * ow0 + i < PW) ? prow[i] : 0.f;
+          const float t = (2 * ow0 + xoff + i < PW) ? prow[i] : 0.f;
           asm("mov.b64 %0, {%1, %1};" : "=l"(v[i]) : "f"(t));
         }
 #pragma unroll
@@ -154,23 +157,34 @@ stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict_
   }
 }
 
-template <typename TOut, bool kU8>
-static cudaError_t stem_launch(const void* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
-                               float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, cudaStream_t s) {
+template <typename TOut, bool kU8, int kStemOC>
+static cudaError_t stem_launch_oc(const void* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
+                                  float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, int pad,
+                                  cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   if ((w & 3) || (h & 1) || (w & 1)) return cudaErrorInvalidValue;
   const int Ho = h / 2;
   size_t smem = (27 * kStemOC + kStemOC + 3 * (2 * kStemTR + 1) * (w + 2)) * sizeof(float);
-  auto kern = stem_kernel<TOut, kU8>;
+  auto kern = stem_kernel<TOut, kU8, kStemOC>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
   dim3 grid((Ho + kStemTR - 1) / kStemTR, n);
   kern<<<grid, kStemThreads, smem, s>>>(x, h, w, wgt, bias, reinterpret_cast<TOut*>(out), sc0, sc1, sc2, sh0, sh1,
-                                        sh2);
+                                        sh2, pad);
   count_launch();
   return cudaGetLastError();
+}
+
+template <typename TOut, bool kU8>
+static cudaError_t stem_launch(const void* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
+                               float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, int oc, int pad,
+                               cudaStream_t s) {
+  if (pad != 0 && pad != 1) return cudaErrorInvalidValue;
+  if (oc == 32) return stem_launch_oc<TOut, kU8, 32>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, pad, s);
+  if (oc == 40) return stem_launch_oc<TOut, kU8, 40>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, pad, s);
+  return cudaErrorInvalidValue;
 }
 
 // debugging aid: B200DF_STEM=simt keeps the CUDA-core stem on the bf16 path
@@ -184,21 +198,23 @@ static bool stem_force_simt() {
 }
 
 cudaError_t launch_stem(const float* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
-                        int dtype, cudaStream_t s) {
-  // the tcgen05 stem gathers with 8-byte loads: images not 8-byte aligned take the SIMT kernel
-  if (dtype == kBF16 && !stem_force_simt() && (reinterpret_cast<uintptr_t>(x) & 7) == 0)
+                        int dtype, cudaStream_t s, int oc, int pad) {
+  // the tcgen05 stem (32 channels, symmetric padding) gathers with 8-byte loads: images not 8-byte aligned
+  // and the 40-channel / TF-same stem of B3 take the SIMT kernel
+  if (dtype == kBF16 && oc == 32 && pad == 1 && !stem_force_simt() && (reinterpret_cast<uintptr_t>(x) & 7) == 0)
     return launch_stem_tc(x, n, h, w, wgt, bias, out, s);
-  if (dtype == kBF16) return stem_launch<bf16, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
-  return stem_launch<float, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
+  if (dtype == kBF16) return stem_launch<bf16, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, oc, pad, s);
+  return stem_launch<float, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, oc, pad, s);
 }
 
 cudaError_t launch_stem_u8(const uint8_t* x, int n, int h, int w, const float* wgt, const float* bias, float sc0,
                            float sc1, float sc2, float sh0, float sh1, float sh2, void* out, int dtype,
-                           cudaStream_t s) {
-  if (dtype == kBF16 && !stem_force_simt())
+                           cudaStream_t s, int oc, int pad) {
+  if (dtype == kBF16 && oc == 32 && pad == 1 && !stem_force_simt())
     return launch_stem_tc_u8(x, n, h, w, wgt, bias, sc0, sc1, sc2, sh0, sh1, sh2, out, s);
-  if (dtype == kBF16) return stem_launch<bf16, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
-  return stem_launch<float, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
+  if (dtype == kBF16) return stem_launch<bf16, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, oc,
+                                                       pad, s);
+  return stem_launch<float, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, oc, pad, s);
 }
 
 }  // namespace b200df

@@ -47,6 +47,9 @@ class Engine:
         self.num_classes = num_classes
         self._h = C.c_void_p()
         _lib.check(self._lib.b200df_create(arch, num_classes, index, C.byref(self._h)))
+        ch, side = C.c_int(), C.c_int()
+        _lib.check(self._lib.b200df_feature_shape(self._h, C.byref(ch), C.byref(side)))
+        self.feature_channels, self.feature_side = int(ch.value), int(side.value)  # Grad-CAM activation A
         self.precision: int | None = None
         self._ws: dict[int, tuple[torch.Tensor, int, int]] = {}
         self._lock = threading.Lock()
@@ -128,7 +131,7 @@ class Engine:
         images = images.contiguous()
         dev = images.device
         logits = torch.empty((n, self.num_classes), dtype=torch.float32, device=dev)
-        low = torch.empty((n, 7, 7), dtype=torch.float32, device=dev)
+        low = torch.empty((n, self.feature_side, self.feature_side), dtype=torch.float32, device=dev)
         cam = torch.empty((n, images.shape[-2], images.shape[-1]), dtype=torch.float32, device=dev) if want_map else None
         if n == 0:
             return logits, low, cam
@@ -145,7 +148,8 @@ class Engine:
         require_cuda_f32(images, "images")
         n = images.shape[0]
         images = images.contiguous()
-        a = torch.empty((n, 1280, 7, 7), dtype=torch.float32, device=images.device)
+        a = torch.empty((n, self.feature_channels, self.feature_side, self.feature_side), dtype=torch.float32,
+                        device=images.device)
         if n == 0:
             return a
         with self._lock, torch.cuda.device(images.device):

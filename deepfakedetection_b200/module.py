@@ -113,6 +113,7 @@ class B200EfficientNetB0(nn.Module):
     """Drop-in for ``timm.create_model("efficientnet_b0", num_classes=...)`` in eval mode on a B200."""
 
     arch_id = _lib.ARCH_EFFICIENTNET_B0
+    arch_name = "efficientnet_b0"
     default_image_size = 224
 
     def __init__(self, num_classes: int = 2, precision: str = "bf16") -> None:
@@ -121,6 +122,14 @@ class B200EfficientNetB0(nn.Module):
             raise ValueError(f"precision must be one of {sorted(PRECISIONS)}, got {precision!r}")
         self.num_classes = num_classes
         self.precision = precision
+        self._build_containers(num_classes)
+        self._init_weights()
+        self._engine = None
+        self._engine_id = 0
+        self._dirty = True
+        self.register_load_state_dict_post_hook(B200EfficientNetB0._post_load)
+
+    def _build_containers(self, num_classes: int) -> None:
         self.conv_stem = _Conv(3, 32, 3, 2, 1, bias=False)
         self.bn1 = _BN(32)
         stages = []
@@ -136,11 +145,9 @@ class B200EfficientNetB0(nn.Module):
         self.conv_head = CamHookPoint(cin, 1280, 1, bias=False)
         self.bn2 = _BN(1280)
         self.classifier = nn.Linear(1280, num_classes)
-        self._init_weights()
-        self._engine = None
-        self._engine_id = 0
-        self._dirty = True
-        self.register_load_state_dict_post_hook(B200EfficientNetB0._post_load)
+
+    def _cam_point(self) -> nn.Module:
+        return self.conv_head
 
     # timm's EfficientNet initialisation, restated: conv N(0, sqrt(2/fan_out)); BN 1/0; linear U(+-1/sqrt(out)).
     def _init_weights(self) -> None:
@@ -209,7 +216,7 @@ class B200EfficientNetB0(nn.Module):
     # ---- the hot call -----------------------------------------------------------------------------------
     def _check_input(self, images: torch.Tensor) -> None:
         if images.ndim != 4 or images.shape[1] != 3 or images.shape[2] != 224 or images.shape[3] != 224:
-            raise ValueError(f"b200 efficientnet_b0 expects float32 [N,3,224,224] images, got {tuple(images.shape)}")
+            raise ValueError(f"b200 {self.arch_name} expects float32 [N,3,224,224] images, got {tuple(images.shape)}")
         if not images.is_cuda:
             raise RuntimeError(
                 f"images are on '{images.device}': the b200 backend has no CPU fallback. The reference silently "
@@ -228,7 +235,7 @@ class B200EfficientNetB0(nn.Module):
             # `.register_hook` on its output, so A must be a graph leaf that requires grad.  The trunk has no
             # backward (inference engine): gradients stop at A, which is all Grad-CAM needs.
             a = ops.trunk(images.detach(), self._engine_id).requires_grad_(True)
-            a = self.conv_head(a)
+            a = self._cam_point()(a)
             return ops.head(a, self._engine_id)
         return ops.forward(images, self._engine_id)
 
@@ -248,3 +255,66 @@ class B200EfficientNetB0(nn.Module):
         if targets is not None:
             targets = targets.to(device=images.device, dtype=torch.int32)
         return ops.forward_cam(images.float(), targets, self._engine_id)
+
+
+# ---- the reference's registry default: efficientnet_pytorch EfficientNet-B3 ---------------------------------------
+
+# (kernel, stride, expand, out channels, repeats): the base table scaled by width 1.2 / depth 1.4
+_B3_STAGES = ((3, 1, 1, 24, 2), (3, 2, 6, 32, 3), (5, 2, 6, 48, 3), (3, 2, 6, 96, 5), (5, 1, 6, 136, 5),
+              (5, 2, 6, 232, 6), (3, 1, 6, 384, 2))
+
+
+class _EPBlock(_NoForward):
+    """efficientnet_pytorch ``MBConvBlock`` parameter names (no ``_expand_conv``/``_bn0`` at expand ratio 1)."""
+
+    def __init__(self, cin: int, cout: int, k: int, stride: int, exp: int) -> None:
+        super().__init__()
+        mid = cin * exp
+        if exp != 1:
+            self._expand_conv = _Conv(cin, mid, 1, bias=False)
+            self._bn0 = _BN(mid, eps=1e-3)
+        self._depthwise_conv = _Conv(mid, mid, k, stride, 0, groups=mid, bias=False)
+        self._bn1 = _BN(mid, eps=1e-3)
+        rd = max(1, int(cin * 0.25))
+        self._se_reduce = _Conv(mid, rd, 1, bias=True)
+        self._se_expand = _Conv(rd, mid, 1, bias=True)
+        self._project_conv = _Conv(mid, cout, 1, bias=False)
+        self._bn2 = _BN(cout, eps=1e-3)
+
+
+class _List(nn.ModuleList):
+    def forward(self, x):  # noqa: D102
+        return _NoForward.forward(self)
+
+
+class B200EfficientNetB3(B200EfficientNetB0):
+    """Drop-in for ``EfficientNet.from_name("efficientnet-b3")`` with a fresh ``_fc``
+    (/root/reference/orchestration/model_registry.py:32-36): the registry's ``efficientnet_b3`` entry (:50-58), the
+    model ``config/inference.yaml`` and the published release weights use.  Parameters carry efficientnet_pytorch's
+    names (``_conv_stem``, ``_bn0``, ``_blocks.N.*``, ``_conv_head``, ``_bn1``, ``_fc``); the engine applies that
+    package's static TF-"same" padding for its 300-pixel native size to the 224-pixel crops and BN eps 1e-3."""
+
+    arch_id = _lib.ARCH_EFFICIENTNET_B3
+    arch_name = "efficientnet_b3"
+
+    def _build_containers(self, num_classes: int) -> None:
+        self._conv_stem = _Conv(3, 40, 3, 2, 0, bias=False)
+        self._bn0 = _BN(40, eps=1e-3)
+        blocks = []
+        cin = 40
+        for k, s, e, cout, reps in _B3_STAGES:
+            for r in range(reps):
+                blocks.append(_EPBlock(cin, cout, k, s if r == 0 else 1, e))
+                cin = cout
+        self._blocks = _List(blocks)
+        self._conv_head = CamHookPoint(cin, 1536, 1, bias=False)
+        self._bn1 = _BN(1536, eps=1e-3)
+        self._fc = nn.Linear(1536, num_classes)
+
+    # B0 exposes `_conv_head` as an alias property; here it is the real submodule of that name
+    @property
+    def _conv_head(self) -> nn.Module:
+        return self._modules["_conv_head"]
+
+    def _cam_point(self) -> nn.Module:
+        return self._modules["_conv_head"]

@@ -51,7 +51,8 @@ def trunk(images: torch.Tensor, engine: int) -> torch.Tensor:
 
 @trunk.register_fake
 def _(images, engine):
-    return images.new_empty((images.shape[0], 1280, 7, 7), dtype=torch.float32)
+    e = _engine(engine)
+    return images.new_empty((images.shape[0], e.feature_channels, e.feature_side, e.feature_side), dtype=torch.float32)
 
 
 @torch.library.custom_op("b200df::head", mutates_args=(), device_types="cuda")
@@ -99,6 +100,6 @@ def _(images, targets, engine):
     n = images.shape[0]
     return (
         images.new_empty((n, _engine(engine).num_classes), dtype=torch.float32),
-        images.new_empty((n, 7, 7), dtype=torch.float32),
+        images.new_empty((n, _engine(engine).feature_side, _engine(engine).feature_side), dtype=torch.float32),
         images.new_empty((n, images.shape[-2], images.shape[-1]), dtype=torch.float32),
     )

@@ -12,6 +12,8 @@ B200 engine module, so ``load_model`` (/root/reference/orchestration/orchestrato
 
 * ``efficientnet_b0``            -- bf16 tcgen05 path (BASELINE.json configs 1-3)
 * ``efficientnet_b0.b200_fp32``  -- strict fp32 path (|dlogit| <= 1e-3 vs the timm fp32 forward)
+* ``efficientnet_b3`` / ``efficientnet_b3.b200_fp32`` -- the registry's own default entry (efficientnet_pytorch
+  layout, model_registry.py:32-36, 50-58), so ``config/inference.yaml`` and the release weights run as they are
 """
 
 from __future__ import annotations
@@ -47,7 +49,27 @@ def build_efficientnet_b0(model_name: str, num_classes: int) -> nn.Module:
     return B200EfficientNetB0(num_classes=num_classes, precision=_precision_for(model_name))
 
 
+def build_efficientnet_b3(model_name: str, num_classes: int) -> nn.Module:
+    """Replaces ``_build_efficientnet`` (model_registry.py:32-36): efficientnet_pytorch ``efficientnet-b3`` layout."""
+    from .module import B200EfficientNetB3
+
+    return B200EfficientNetB3(num_classes=num_classes, precision=_precision_for(model_name))
+
+
 SERVED: dict[str, dict[str, Any]] = {
+    # the reference's own exact entry (model_registry.py:50-58), same train_module / weights_key / image size
+    "efficientnet_b3": {
+        "train_module": "trainers.efficientnet",
+        "weights_key": "efficientnet_b3",
+        "default_image_size": 224,
+        "builder": build_efficientnet_b3,
+    },
+    "efficientnet_b3.b200_fp32": {
+        "train_module": "trainers.efficientnet",
+        "weights_key": "efficientnet_b3",
+        "default_image_size": 224,
+        "builder": build_efficientnet_b3,
+    },
     "efficientnet_b0": {
         "train_module": "trainers.efficientnet",
         "weights_key": "efficientnet_b0",

@@ -51,7 +51,9 @@ extern "C" {
 #define B200DF_E_WORKSPACE (-5) /* workspace too small or misaligned                  */
 
 /* architectures */
-#define B200DF_ARCH_EFFICIENTNET_B0 0
+#define B200DF_ARCH_EFFICIENTNET_B0 0 /* timm `efficientnet_b0` state_dict layout (conv_stem, blocks.S.R.*, ...)     */
+#define B200DF_ARCH_EFFICIENTNET_B3 1 /* efficientnet_pytorch `efficientnet-b3` layout (_conv_stem, _blocks.N.*, _fc): */
+                                      /* the reference's registry default, orchestration/model_registry.py:32-36,50-58 */
 
 /* precisions (b200df_finalize) */
 #define B200DF_PREC_BF16 0 /* bf16 NHWC activations/weights, fp32 accumulate, tcgen05 GEMMs */
@@ -78,6 +80,10 @@ int b200df_set_tensor(b200df_handle h, const char* name, const float* data, size
 /* Number of tensors the architecture expects / name+numel of the i-th one. */
 int b200df_num_tensors(b200df_handle h);
 int b200df_tensor_info(b200df_handle h, int index, const char** name, size_t* numel);
+
+/* Shape of the Grad-CAM activation A (raw conv_head / _conv_head output, web_ui.py:108-110) for one image:
+ * channels (1280 for B0, 1536 for B3) and the square spatial side (7 at 224 x 224 input). */
+int b200df_feature_shape(b200df_handle h, int* channels, int* side);
 
 /* Fold BN into conv weights (fp32, on the host), convert to `precision`, lay out for the
  * kernels and upload.  May be called again after further set_tensor calls. */

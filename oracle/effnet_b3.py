@@ -209,6 +209,23 @@ def make_calibrated_oracle(seed: int = 0, num_classes: int = 2, calib_n: int = 1
     return model
 
 
+def make_seeded_oracle(seed: int = 0, num_classes: int = 2) -> EfficientNetB3Oracle:
+    """BASELINE.json's parity recipe on the B3 layout (same as oracle/effnet_b0.make_seeded_oracle): default init,
+    then randomised BN statistics/affine, SE biases and classifier.  Deterministic given ``seed``."""
+    from .effnet_b0 import randomize_bn_, randomize_head_
+
+    g = torch.Generator().manual_seed(seed)
+    prev = torch.random.get_rng_state()
+    torch.manual_seed(seed)
+    try:
+        model = EfficientNetB3Oracle(num_classes)
+    finally:
+        torch.random.set_rng_state(prev)
+    randomize_bn_(model, g)
+    randomize_head_(model, g)
+    return model.eval()
+
+
 def to_torchvision_state_dict(sd: dict[str, torch.Tensor]) -> dict[str, torch.Tensor]:
     """Map efficientnet_pytorch keys onto torchvision.models.efficientnet_b3 keys."""
     blocks = b3_blocks()

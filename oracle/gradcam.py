@@ -42,7 +42,8 @@ def postprocess_cam(cam_lowres: torch.Tensor, out_hw: tuple[int, int]) -> torch.
 
 
 def gradcam_autograd(model, images: torch.Tensor, targets: torch.Tensor):
-    """Hook-and-backward Grad-CAM on ``model.conv_head``.
+    """Hook-and-backward Grad-CAM on the layer the reference's target rule picks (/root/reference/web_ui.py:108-110):
+    ``model._conv_head`` when it exists (efficientnet_pytorch layout), else ``model.conv_head`` (timm layout).
 
     Returns (logits [N,C], cam_lowres [N,h,w] after ReLU, cam [N,H,W] in [0,1]).
     """
@@ -52,7 +53,10 @@ def gradcam_autograd(model, images: torch.Tensor, targets: torch.Tensor):
         store["A"] = out
         out.register_hook(lambda g: store.__setitem__("G", g))
 
-    handle = model.conv_head.register_forward_hook(hook)
+    target = getattr(model, "_conv_head", None)
+    if target is None:
+        target = model.conv_head
+    handle = target.register_forward_hook(hook)
     try:
         with torch.enable_grad():
             model.zero_grad(set_to_none=True)
