@@ -47,10 +47,10 @@ cudaError_t launch_stem_u8(const uint8_t* x_hwc, int n, int h, int w, const floa
 typedef long long pool_t;
 // bf16 output only: implicit GEMM on tcgen05 (stem_tc.cu); launch_stem / launch_stem_u8 dispatch to these
 cudaError_t launch_stem_tc(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias, void* out,
-                           cudaStream_t s);
+                           cudaStream_t s, int oc = 32, int pad = 1);
 cudaError_t launch_stem_tc_u8(const uint8_t* x_hwc, int n, int h, int w, const float* wgt, const float* bias,
                               float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, void* out,
-                              cudaStream_t s);
+                              cudaStream_t s, int oc = 32, int pad = 1);
 
 // pad_lo: zero rows/columns BEFORE the image; -1 = symmetric (k-1)/2.  The pad after is k - 1 - pad_lo, so the
 // output size (h - 1) / stride + 1 does not depend on it (efficientnet_pytorch Conv2dStaticSamePadding).

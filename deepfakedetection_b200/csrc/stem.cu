@@ -199,10 +199,10 @@ static bool stem_force_simt() {
 
 cudaError_t launch_stem(const float* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
                         int dtype, cudaStream_t s, int oc, int pad) {
-  // the tcgen05 stem (32 channels, symmetric padding) gathers with 8-byte loads: images not 8-byte aligned
-  // and the 40-channel / TF-same stem of B3 take the SIMT kernel
-  if (dtype == kBF16 && oc == 32 && pad == 1 && !stem_force_simt() && (reinterpret_cast<uintptr_t>(x) & 7) == 0)
-    return launch_stem_tc(x, n, h, w, wgt, bias, out, s);
+  // the tcgen05 stem gathers with 8-byte loads: images not 8-byte aligned take the SIMT kernel
+  if (dtype == kBF16 && ((oc == 32 && pad == 1) || (oc == 40 && pad == 0)) && !stem_force_simt() &&
+      (reinterpret_cast<uintptr_t>(x) & 7) == 0)
+    return launch_stem_tc(x, n, h, w, wgt, bias, out, s, oc, pad);
   if (dtype == kBF16) return stem_launch<bf16, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, oc, pad, s);
   return stem_launch<float, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, oc, pad, s);
 }
@@ -210,8 +210,8 @@ cudaError_t launch_stem(const float* x, int n, int h, int w, const float* wgt, c
 cudaError_t launch_stem_u8(const uint8_t* x, int n, int h, int w, const float* wgt, const float* bias, float sc0,
                            float sc1, float sc2, float sh0, float sh1, float sh2, void* out, int dtype,
                            cudaStream_t s, int oc, int pad) {
-  if (dtype == kBF16 && oc == 32 && pad == 1 && !stem_force_simt())
-    return launch_stem_tc_u8(x, n, h, w, wgt, bias, sc0, sc1, sc2, sh0, sh1, sh2, out, s);
+  if (dtype == kBF16 && ((oc == 32 && pad == 1) || (oc == 40 && pad == 0)) && !stem_force_simt())
+    return launch_stem_tc_u8(x, n, h, w, wgt, bias, sc0, sc1, sc2, sh0, sh1, sh2, out, s, oc, pad);
   if (dtype == kBF16) return stem_launch<bf16, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, oc,
                                                        pad, s);
   return stem_launch<float, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, oc, pad, s);

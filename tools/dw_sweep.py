@@ -13,6 +13,10 @@ only = sys.argv[2] if len(sys.argv) > 2 else None
 # (h_in, channels, k, stride)
 LAYERS = [(112, 32, 3, 1), (112, 96, 3, 2), (56, 144, 3, 1), (56, 144, 5, 2), (28, 240, 5, 1), (28, 240, 3, 2),
           (14, 480, 3, 1), (14, 480, 5, 1), (14, 672, 5, 1), (14, 672, 5, 2), (7, 1152, 5, 1), (7, 1152, 3, 1)]
+if os.environ.get("DW_SWEEP_MODEL") == "b3":  # the EfficientNet-B3 (efficientnet_pytorch) depthwise shapes
+    LAYERS = [(112, 40, 3, 1), (112, 24, 3, 1), (112, 144, 3, 2), (56, 192, 3, 1), (56, 192, 5, 2), (28, 288, 5, 1),
+              (28, 288, 3, 2), (14, 576, 3, 1), (14, 576, 5, 1), (14, 816, 5, 1), (14, 816, 5, 2), (7, 1392, 5, 1),
+              (7, 1392, 3, 1), (7, 2304, 3, 1)]
 lib = _lib.lib()
 P = lambda t: C.c_void_p(t.data_ptr())
 dev = "cuda"

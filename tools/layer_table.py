@@ -8,7 +8,8 @@ from deepfakedetection_b200 import registry
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 prec = sys.argv[2] if len(sys.argv) > 2 else "bf16"
-name = "efficientnet_b0" if prec == "bf16" else "efficientnet_b0.b200_fp32"
+arch = sys.argv[3] if len(sys.argv) > 3 else "efficientnet_b0"
+name = arch if prec == "bf16" else arch + ".b200_fp32"
 m = registry.get_model_spec(name).builder(name, 2)
 synth_state(m)
 m.to("cuda").eval()

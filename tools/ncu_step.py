@@ -8,7 +8,8 @@ from deepfakedetection_b200 import registry
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 cam = len(sys.argv) > 2 and sys.argv[2] == "cam"
-m = registry.get_model_spec("efficientnet_b0").builder("efficientnet_b0", 2)
+arch = sys.argv[3] if len(sys.argv) > 3 else "efficientnet_b0"
+m = registry.get_model_spec(arch).builder(arch, 2)
 synth_state(m)
 m.to("cuda").eval()
 x = torch.randn(n, 3, 224, 224, device="cuda")

@@ -63,5 +63,50 @@ def step(path: str) -> None:
         print(f"{n:3d} {short(r[idx['Kernel Name']])[:44]:44s} " + " ".join(vals))
 
 
+def details(path: str) -> None:
+    """Long-form CSV (ncu --set full --csv without --page raw: one metric per row) -> one line per launch."""
+    rows = [r for r in csv.reader(open(path, errors="ignore")) if len(r) > 14]
+    hdr = rows[0]
+    idx = {h: i for i, h in enumerate(hdr)}
+    want = [("Duration", "us", 8), ("DRAM Throughput", "dram%", 6), ("Compute (SM) Throughput", "sm%", 6),
+            ("Issue Slots Busy", "issue%", 6), ("Achieved Occupancy", "occ%", 6), ("Registers Per Thread", "regs", 5),
+            ("Grid Size", "grid", 6), ("Block Size", "blk", 5)]
+    per: dict[int, dict] = {}
+    for r in rows[1:]:
+        try:
+            k = int(r[idx["ID"]])
+        except ValueError:
+            continue
+        d = per.setdefault(k, {"name": r[idx["Kernel Name"]]})
+        nm = r[idx["Metric Name"]]
+        if nm not in d:
+            val, unit = r[idx["Metric Value"]].replace(",", ""), r[idx["Metric Unit"]]
+            if nm == "Duration":
+                try:
+                    val = f"{float(val) * {'ns': 1e-3, 'us': 1.0, 'ms': 1e3, 'msecond': 1e3, 'usecond': 1.0, 'nsecond': 1e-3}.get(unit, 1.0):.1f}"
+                except ValueError:
+                    pass
+            d[nm] = val
+    print("# one forward step (N=256, bf16), ncu --set full --clock-control none (details page, one line per launch)")
+    print(f"{'#':>3s} {'kernel':44s} " + " ".join(f"{c[1]:>{c[2]}s}" for c in want))
+    tot = 0.0
+    for k in sorted(per):
+        d = per[k]
+        vals = []
+        for key, _, w in want:
+            v = d.get(key, "-")
+            try:
+                v = f"{float(v):.1f}" if "." in v else v
+            except ValueError:
+                pass
+            vals.append(f"{v:>{w}s}")
+        try:
+            tot += float(d.get("Duration", 0))
+        except ValueError:
+            pass
+        print(f"{k:3d} {short(d['name'])[:44]:44s} " + " ".join(vals))
+    print(f"# sum of durations: {tot / 1e3:.3f} ms over {len(per)} launches")
+
+
 if __name__ == "__main__":
-    {"launches": launches, "step": step}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "step": step, "details": details}[sys.argv[1]](sys.argv[2])
