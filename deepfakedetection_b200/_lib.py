@@ -57,6 +57,8 @@ SIGNATURES: dict[str, tuple] = {
     "b200df_profile_get": (_i, [_vp, _i, C.POINTER(C.c_char_p), C.POINTER(_f), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "b200df_profile_reset": (_i, [_vp]),
     "b200df_k_stem": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
+    "b200df_k_stem_ex": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "b200df_k_dwconv_ex": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp]),
     "b200df_k_dwconv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp]),
     "b200df_k_se": (_i, [_vp, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _vp]),
     "b200df_k_pwconv": (_i, [_vp, _ll, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _vp]),

@@ -901,6 +901,19 @@ extern "C" int b200df_k_stem(const float* x_nchw, int n, int h, int w, const flo
   return B200DF_OK;
 }
 
+extern "C" int b200df_k_stem_ex(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias, void* out,
+                                int dtype, int oc, int pad, void* stream) {
+  CU_OK(launch_stem(x_nchw, n, h, w, wgt, bias, out, dtype, S(stream), oc, pad));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_dwconv_ex(const void* x, int n, int h, int w, int c, int k, int stride, int pad_lo,
+                                  const float* wgt, const float* bias, void* out, long long* pool, int dtype,
+                                  void* stream) {
+  CU_OK(launch_dwconv(x, n, h, w, c, k, stride, wgt, bias, out, pool, dtype, S(stream), pad_lo));
+  return B200DF_OK;
+}
+
 extern "C" int b200df_k_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
                                const float* bias, void* out, long long* pool, int dtype, void* stream) {
   CU_OK(launch_dwconv(x, n, h, w, c, k, stride, wgt, bias, out, pool, dtype, S(stream)));

@@ -174,12 +174,23 @@ int b200df_profile_reset(b200df_handle h);
 int b200df_k_stem(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias,
                   void* out, int dtype, void* stream);
 
+/* Same with `oc` output channels (32 | 40) and `pad` zero rows/columns BEFORE the image: 1 = symmetric,
+ * 0 = the static TF-"same" split (0, 1) of efficientnet_pytorch's Conv2dStaticSamePadding (its stem at the
+ * 300-pixel native size; /root/reference/orchestration/model_registry.py:32-36).  out: [n,H/2,W/2,oc]. */
+int b200df_k_stem_ex(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias,
+                     void* out, int dtype, int oc, int pad, void* stream);
+
 /* Depthwise kxk (k=3|5, stride 1|2, pad (k-1)/2) + bias + SiLU; optional pooled sums
  * pool[n,c] += sum_hw(out) (must be zeroed by the caller) as Q24 fixed-point int64 (value * 2^24),
  * accumulated with integer atomics so the sums are order-independent and bit-reproducible.
  * wgt: [k*k, c] fp32 (tap-major). */
 int b200df_k_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
                     const float* bias, void* out, long long* pool, int dtype, void* stream);
+
+/* Same with an explicit pad-before `pad_lo` (pad after = k - 1 - pad_lo; -1 = symmetric): the TF-"same" 3x3
+ * stride-2 layers of the efficientnet_pytorch layout use pad_lo = 0.  Output size (h - 1) / stride + 1. */
+int b200df_k_dwconv_ex(const void* x, int n, int h, int w, int c, int k, int stride, int pad_lo, const float* wgt,
+                       const float* bias, void* out, long long* pool, int dtype, void* stream);
 
 /* Squeeze-excite MLP on pooled sums: gate[n,c] = sigmoid(W2 silu(W1 (pool*inv_hw) + b1) + b2).
  * w1: conv_reduce [rd,c]; w2t: conv_expand TRANSPOSED to [rd,c]. */

@@ -26,6 +26,23 @@ def k_stem(x, w, b, dt):
     return out
 
 
+def k_stem_ex(x, w, b, dt, oc, pad):
+    n, _, h, wd = x.shape
+    out = torch.empty((n, h // 2, wd // 2, oc), dtype=tdtype(dt), device=x.device)
+    _lib.check(_lib.lib().b200df_k_stem_ex(P(x), n, h, wd, P(w), P(b), P(out), dt, oc, pad, stream()))
+    return out
+
+
+def k_dwconv_ex(x, w_tap_major, bias, k, stride, pad_lo, dt):
+    n, h, wd, c = x.shape
+    ho, wo = (h - 1) // stride + 1, (wd - 1) // stride + 1
+    out = torch.empty((n, ho, wo, c), dtype=tdtype(dt), device=x.device)
+    pl = torch.zeros((n, c), dtype=torch.int64, device=x.device)
+    _lib.check(_lib.lib().b200df_k_dwconv_ex(P(x), n, h, wd, c, k, stride, pad_lo, P(w_tap_major), P(bias), P(out),
+                                             P(pl), dt, stream()))
+    return out, (pl.double() / 2.0**24).float()
+
+
 def k_dwconv(x, w_tap_major, bias, k, stride, dt, pool=True):
     n, h, wd, c = x.shape
     pad = (k - 1) // 2

@@ -42,6 +42,46 @@ def test_stem(dt):
     torch.testing.assert_close(out, ref, **tol(dt))
 
 
+@pytest.mark.parametrize("dt", [FP, BF])
+@pytest.mark.parametrize("hw", [(224, 224), (64, 96)])
+def test_stem_40_channels_tf_same_padding(dt, hw):
+    """EfficientNet-B3 (efficientnet_pytorch) stem: 40 channels, static TF-"same" pad (0, 1) -- the SIMT kernel on the
+    fp32 path, the tcgen05 implicit GEMM (N = 48) on the bf16 path."""
+    from gpu_util import k_stem_ex
+
+    g = gen(40)
+    h, wd = hw
+    x = torch.randn(3, 3, h, wd, device="cuda", generator=g)
+    w = torch.randn(40, 3, 3, 3, device="cuda", generator=g) * 0.2
+    b = torch.randn(40, device="cuda", generator=g) * 0.1
+    xr, wr = (x.bfloat16().float(), w.bfloat16().float()) if dt == BF else (x, w)
+    ref = F.silu(F.conv2d(F.pad(xr, (0, 1, 0, 1)), wr, b, stride=2)).permute(0, 2, 3, 1)
+    out = k_stem_ex(x, w.reshape(40, 27).contiguous(), b, dt, 40, 0).float()
+    torch.testing.assert_close(out, ref, **tol(dt))
+
+
+# the 3x3 stride-2 depthwise layers of B3 (pad (0, 1)) + ragged / odd sizes (odd sizes take the plain kernel)
+DW_TFSAME_CASES = [(144, 112), (288, 28), (40, 56), (24, 16), (8, 9), (16, 13)]
+
+
+@pytest.mark.parametrize("dt", [FP, BF])
+@pytest.mark.parametrize("c,h", DW_TFSAME_CASES)
+def test_dwconv_tf_same_padding(c, h, dt):
+    from gpu_util import k_dwconv_ex, tdtype
+
+    g = gen(c * 7 + h)
+    n = 3 if h > 60 else 5
+    x = torch.randn(n, h, h, c, device="cuda", generator=g).to(tdtype(dt))
+    w = torch.randn(c, 1, 3, 3, device="cuda", generator=g) * 0.3
+    b = torch.randn(c, device="cuda", generator=g) * 0.1
+    xp = F.pad(x.float().permute(0, 3, 1, 2), (0, 2, 0, 2))  # (0, 1) is what the layer needs at even sizes; odd sizes
+    ho = (h - 1) // 2 + 1                                    # use their own last tap: crop to the kernel's output size
+    ref = F.silu(F.conv2d(xp, w, b, stride=2, groups=c))[:, :, :ho, :ho]
+    out, pool = k_dwconv_ex(x, w.reshape(c, 9).t().contiguous(), b, 3, 2, 0, dt)
+    torch.testing.assert_close(out.float(), ref.permute(0, 2, 3, 1), **tol(dt))
+    torch.testing.assert_close(pool, ref.sum((2, 3)), atol=5e-2 if dt == BF else 2e-3, rtol=2e-3 if dt == BF else 1e-4)
+
+
 # (C, H, k, stride) for the 16 depthwise layers of B0 (deduplicated) + ragged extras
 DW_CASES = [(32, 112, 3, 1), (96, 112, 3, 2), (144, 56, 3, 1), (144, 56, 5, 2), (240, 28, 5, 1), (240, 28, 3, 2),
             (480, 14, 3, 1), (480, 14, 5, 1), (672, 14, 5, 1), (672, 14, 5, 2), (1152, 7, 5, 1), (1152, 7, 3, 1),
