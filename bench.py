@@ -225,8 +225,12 @@ def run_b200(args) -> None:
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"   # NCCL prints its version banner to STDOUT; keep stdout = one JSON line
+        # NCCL prints its version banner to STDOUT (fd 1, from C) when the communicator comes up, whatever
+        # NCCL_DEBUG says on this build: park the real stdout and point fd 1 at stderr until the JSON line is written
+        global _JSON_FD
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
 
     name = args.model if args.precision == "bf16" else args.model + ".b200_fp32"
@@ -369,6 +373,19 @@ def run_e2e(model, step, B, K, W, dev, rank, world, local, u8: bool = False):
                     % (in_bytes * K / (ms * 1e-3) / 1e9)}
 
 
+_JSON_FD = None  # the real stdout while fd 1 is parked on stderr (multi-GPU runs)
+
+
+def emit(line: dict) -> None:
+    text = json.dumps(line) + "\n"
+    if _JSON_FD is None:
+        sys.stdout.write(text)
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_JSON_FD, text.encode())
+
+
 def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, clocks, model, e2e_u8=None) -> None:
     import torch
 
@@ -425,7 +442,7 @@ def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, 
         line["cpu_baseline"] = {"value": round(ips, 2), "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{steps_cpu} timed steps x 64 images (+2 warm-up), oracle/{args.model.replace('efficientnet', 'effnet')}.py fp32 eager, "
                                           f"torch threads={cores}, os.cpu_count={os.cpu_count()}"}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main() -> None:
