@@ -208,6 +208,29 @@ def run_reference(args) -> None:
     print(json.dumps(line), flush=True)
 
 
+def bind_to_gpu_numa_node(local: int) -> None:
+    """Pin this rank's host threads to the CPUs next to its GPU (NVML's ideal-CPU mask) BEFORE any pinned buffer is
+    allocated, so first-touch puts the staging memory on the GPU's NUMA node and H2D copies do not cross sockets.
+    Host plumbing only; silently skipped where NVML or the cpuset does not allow it."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[local]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else local
+        h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64 + 4)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        want = cpus & allowed
+        if want and want != allowed:
+            os.sched_setaffinity(0, want)
+        print(f"[bench] rank-local GPU {idx}: ideal CPUs {len(cpus)}, allowed {len(allowed)}, bound to {len(want) or len(allowed)}",
+              file=sys.stderr)
+    except Exception as ex:  # noqa: BLE001 - optional
+        print(f"[bench] NUMA binding skipped: {ex}", file=sys.stderr)
+
+
 # ---- our arm ----------------------------------------------------------------------------------------------
 def run_b200(args) -> None:
     import torch
@@ -223,6 +246,8 @@ def run_b200(args) -> None:
         raise SystemExit("bench.py: no sm_100 device visible -- the b200 backend has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    if world > 1:
+        bind_to_gpu_numa_node(local)   # N = 1 keeps every host core for the cpu_baseline leg
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # NCCL prints its version banner to STDOUT (fd 1, from C) when the communicator comes up, whatever
@@ -435,7 +460,7 @@ def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, 
         line["e2e"] = e2e
     if e2e_u8 is not None:  # extra, not the headline: same metric fed with uint8 crops (4x fewer PCIe bytes)
         line["e2e_u8"] = e2e_u8
-    if not args.no_cpu_baseline and world >= 1:
+    if not args.no_cpu_baseline and world == 1:  # rank 0 at N=1 only
         steps_cpu = 6
         ips, ms, cores = cpu_eval_images_per_s({k: v.cpu() for k, v in model.state_dict().items()}, 64, steps_cpu, 2,
                                                arch=args.model)
