@@ -178,3 +178,19 @@ def test_b3_gradcam_hook_protocol_like_web_ui(calibrated):
             gray = cam(input_tensor=one.cuda(), targets=[ClassifierOutputTarget(cls_idx)])[0]
         assert gray.shape == (224, 224) and gray.dtype == np.float32
         assert _cos(torch.from_numpy(gray)[None], cam_ref).item() >= MIN_CAM_COSINE, f"use_hooks={use_hooks}"
+
+
+def test_b3_golden_vectors(recipe):
+    """The strict fp32 engine against the committed vectors (tests/golden/effnet_b3_seed0.npz)."""
+    from pathlib import Path
+
+    from oracle.effnet_b0 import synth_images
+
+    golden = np.load(Path(__file__).resolve().parent / "golden" / "effnet_b3_seed0.npz")
+    ref_model, _, _ = recipe
+    model = build(ref_model, "efficientnet_b3.b200_fp32")
+    x = synth_images(4, seed=123)
+    logits, low, cam = model.forward_cam(x.cuda(), torch.from_numpy(golden["targets"]))
+    np.testing.assert_allclose(logits.cpu().numpy(), golden["logits"], atol=TOL_FP32_LOGIT)
+    assert _cos(low.cpu(), torch.from_numpy(golden["cam_low"])).min().item() >= MIN_CAM_COSINE
+    assert _cos(cam.cpu()[:, ::8, ::8], torch.from_numpy(golden["cam_ds"])).min().item() >= MIN_CAM_COSINE

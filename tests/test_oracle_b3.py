@@ -1,9 +1,13 @@
 """Pins the EfficientNet-B3 (efficientnet_pytorch layout) oracle: architecture against torchvision's independently
 written efficientnet_b3, static-same padding against its formula and an explicit pad + valid conv (CPU only)."""
 
+from pathlib import Path
+
 import pytest
 import torch
 from torch.nn import functional as F
+
+ROOT = Path(__file__).resolve().parent.parent
 
 from oracle import effnet_b3 as o3
 from oracle.effnet_b0 import synth_images
@@ -63,3 +67,28 @@ def test_matches_torchvision_b3_with_symmetric_padding():
         a, b = model(x), ref(x)
     assert torch.allclose(a, b, rtol=0, atol=2e-5), (a - b).abs().max()
     assert a.std() > 0.1
+
+
+def test_b3_oracle_matches_golden():
+    """Committed vectors (tests/golden/make_golden_b3.py) guard the oracle, its pads and the weight recipe."""
+    import numpy as np
+
+    from oracle.effnet_b0 import synth_images
+    from oracle.effnet_b3 import make_seeded_oracle
+    from oracle.gradcam import gradcam_autograd
+
+    golden = np.load(ROOT / "tests" / "golden" / "effnet_b3_seed0.npz")
+    model = make_seeded_oracle(seed=0)
+    x = synth_images(4, seed=123)
+    np.testing.assert_allclose(x.double().sum((1, 2, 3)).numpy(), golden["x_checksum"], rtol=1e-9)
+    sd = model.state_dict()
+    w = np.array([float(sd[k].double().abs().sum()) for k in sorted(sd) if "num_batches" not in k])
+    np.testing.assert_allclose(w, golden["w_checksum"], rtol=2e-4)
+    with torch.no_grad():
+        logits = model(x)
+        a = model.forward_features_raw(x)
+    np.testing.assert_allclose(logits.numpy(), golden["logits"], atol=1e-4)
+    np.testing.assert_allclose(a.mean((2, 3)).numpy(), golden["a_mean"], atol=1e-4)
+    _, cam_low, cam = gradcam_autograd(model, x, torch.from_numpy(golden["targets"]))
+    np.testing.assert_allclose(cam_low.numpy(), golden["cam_low"], atol=1e-5)
+    np.testing.assert_allclose(cam[:, ::8, ::8].numpy(), golden["cam_ds"], atol=2e-3)
