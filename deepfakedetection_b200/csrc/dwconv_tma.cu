@@ -427,6 +427,9 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
       if (t.h == h && h == w && t.k == k && t.stride == stride) {
         f_th = t.th; f_otw = t.otw; f_m = t.m; f_g = t.g; nc = t.nc;
       }
+    // EfficientNet-B3's wider 7^2 layers (C = 1392 / 2304) prefer other image-group sizes (DW_SWEEP_MODEL=b3
+    // tools/dw_sweep.py, profiles/r01_h_dw_sweep_b3.txt): 5x5 g = 2 (0.048 -> 0.043 ms), 3x3 C=1392 g = 1, C=2304 g = 8
+    if (h == 7 && w == 7 && stride == 1 && c > 1152 && f_th) f_g = k == 5 ? 2 : (c >= 2304 ? 8 : 1);
   }
   if (nc != 1 && (nc != 2 || stride != 1 || (k == 5 && f_th == 8))) return -1;
   double best_score = -1.0;

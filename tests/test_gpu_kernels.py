@@ -85,7 +85,10 @@ def test_dwconv_tf_same_padding(c, h, dt):
 # (C, H, k, stride) for the 16 depthwise layers of B0 (deduplicated) + ragged extras
 DW_CASES = [(32, 112, 3, 1), (96, 112, 3, 2), (144, 56, 3, 1), (144, 56, 5, 2), (240, 28, 5, 1), (240, 28, 3, 2),
             (480, 14, 3, 1), (480, 14, 5, 1), (672, 14, 5, 1), (672, 14, 5, 2), (1152, 7, 5, 1), (1152, 7, 3, 1),
-            (8, 9, 3, 1), (16, 13, 5, 2), (24, 5, 3, 2)]
+            (8, 9, 3, 1), (16, 13, 5, 2), (24, 5, 3, 2),
+            # EfficientNet-B3 shapes (symmetric-pad layers; the pad-(0,1) ones are in DW_TFSAME_CASES)
+            (40, 112, 3, 1), (24, 112, 3, 1), (192, 56, 3, 1), (192, 56, 5, 2), (288, 28, 5, 1), (576, 14, 3, 1),
+            (816, 14, 5, 1), (816, 14, 5, 2), (1392, 7, 5, 1), (1392, 7, 3, 1), (2304, 7, 3, 1)]
 
 
 @pytest.mark.parametrize("dt", [FP, BF])
