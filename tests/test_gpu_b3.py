@@ -194,3 +194,23 @@ def test_b3_golden_vectors(recipe):
     np.testing.assert_allclose(logits.cpu().numpy(), golden["logits"], atol=TOL_FP32_LOGIT)
     assert _cos(low.cpu(), torch.from_numpy(golden["cam_low"])).min().item() >= MIN_CAM_COSINE
     assert _cos(cam.cpu()[:, ::8, ::8], torch.from_numpy(golden["cam_ds"])).min().item() >= MIN_CAM_COSINE
+
+
+def test_b3_u8_input_path_on_the_tcgen05_stem(recipe):
+    """bf16 engine: uint8 crops through the 40-channel TF-same tcgen05 stem (ToTensor + Normalize fused into the
+    gather) against the same engine fed the host-normalised fp32 tensor."""
+    ref_model, _, ref = recipe
+    model = build(ref_model, "efficientnet_b3")
+    g = torch.Generator().manual_seed(6)
+    u8 = torch.randint(0, 256, (9, 224, 224, 3), dtype=torch.uint8, generator=g)
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    f = (u8.float() / 255.0 - torch.tensor(mean)) / torch.tensor(std)
+    with torch.inference_mode():
+        a = model(f.permute(0, 3, 1, 2).contiguous().cuda()).cpu()
+        b = model.forward_u8(u8.cuda(), mean, std).cpu()
+        c = model.forward_u8(u8.cuda(), None, None).cpu()   # val_normalize: false -> ToTensor only
+        d = model((u8.float() / 255.0).permute(0, 3, 1, 2).contiguous().cuda()).cpu()
+    assert torch.isfinite(b).all() and torch.isfinite(c).all()
+    assert (a - b).pow(2).mean().sqrt().item() <= 0.05 * ref.std().item()
+    assert (c - d).pow(2).mean().sqrt().item() <= 0.05 * ref.std().item()
+    assert (torch.softmax(a, 1) - torch.softmax(b, 1)).abs().max().item() <= TOL_BF16_SOFTMAX
