@@ -21,6 +21,9 @@ OK = 0
 E_INVALID, E_STATE, E_CUDA, E_NO_DEVICE, E_WORKSPACE = -1, -2, -3, -4, -5
 ARCH_EFFICIENTNET_B0 = 0
 ARCH_EFFICIENTNET_B3 = 1
+ARCH_EFFICIENTFORMERV2_S1 = 2
+ARCH_FASTERVIT_0 = 3
+ARCH_FASTERVIT_2 = 4
 PREC_BF16, PREC_FP32 = 0, 1
 DT_BF16, DT_FP32 = 0, 1
 
@@ -45,11 +48,16 @@ SIGNATURES: dict[str, tuple] = {
     "b200df_trunk": (_i, [_vp, _vp, _i, _vp, _vp, _sz, _vp]),
     "b200df_head": (_i, [_vp, _vp, _i, _vp, _vp]),
     "b200df_head_backward": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "b200df_trunk_ex": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _sz, _vp]),
+    "b200df_head_ex": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "b200df_softmax_pack": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "b200df_cam_overlay": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, C.c_float, _vp, _vp]),
     "b200df_threshold_hist": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp]),
     "b200df_confusion_matrix": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "b200df_auc_counts": (_i, [_vp, _i, _vp, _i, _vp, _vp]),
+    "b200df_debug_num_marks": (_i, [_vp]),
+    "b200df_debug_mark": (_i, [_vp, _i, _i, C.POINTER(C.c_char_p), C.POINTER(_i), C.POINTER(_i * 4), C.POINTER(_sz)]),
+    "b200df_debug_stop_after": (_i, [_vp, _i]),
     "b200df_launch_count": (_ll, []),
     "b200df_reset_launch_count": (None, []),
     "b200df_set_profile": (_i, [_vp, _i]),

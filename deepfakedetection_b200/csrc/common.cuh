@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "act.h"
+
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
 #error "b200df kernels are written for sm_100a (Blackwell) only"
 #endif
@@ -43,6 +45,33 @@ template <bool kFast>
 __device__ __forceinline__ float silu(float x) {
   if constexpr (kFast) return silu_fast(x);
   else return silu_acc(x);
+}
+
+// GELU (nn.GELU default = exact erf form).  Accurate: erff.  Fast (bf16 path): the tanh form
+//   gelu(x) = h + h*tanh(h*(1.5957691216 + 0.2854191951*h^2)), h = x/2
+// (|tanh form - erf form| <= 4.8e-4 absolute, an order of magnitude below one bf16 ulp of the stored result).
+__device__ __forceinline__ float gelu_acc(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float h = 0.5f * x;
+  const float u = h * fmaf(0.2854191951f, h * h, 1.5957691216f);
+  return fmaf(h, tanh_fast(u), h);
+}
+
+template <bool kFast>
+__device__ __forceinline__ float apply_act(float x, int act) {
+  switch (act) {
+    case kActSiLU: return silu<kFast>(x);
+    case kActGELU: return kFast ? gelu_fast(x) : gelu_acc(x);
+    case kActReLU: return fmaxf(x, 0.f);
+    default: return x;
+  }
+}
+template <int ACT, bool kFast>
+__device__ __forceinline__ float act_fn(float x) {
+  if constexpr (ACT == kActSiLU) return silu<kFast>(x);
+  else if constexpr (ACT == kActGELU) return kFast ? gelu_fast(x) : gelu_acc(x);
+  else if constexpr (ACT == kActReLU) return fmaxf(x, 0.f);
+  else return x;
 }
 
 // ---- 8-channel vector access (NHWC, C % 8 == 0) ---------------------------------------------
@@ -103,6 +132,13 @@ __device__ __forceinline__ void store8<float>(float* __restrict__ p, const float
 
 template <typename T> struct is_bf16 { static constexpr bool value = false; };
 template <> struct is_bf16<bf16> { static constexpr bool value = true; };
+
+template <typename T> __device__ __forceinline__ float to_f(T v);
+template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f<bf16>(bf16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
 
 // ---- deterministic pooled sums ----------------------------------------------------------------
 // SE pool sums are accumulated across CTAs with 64-bit INTEGER atomics on a Q24 fixed-point value

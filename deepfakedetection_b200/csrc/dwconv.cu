@@ -19,7 +19,8 @@ constexpr int kDwThreads = 256;
 template <typename T, int K, int S, int TW>
 __global__ void __launch_bounds__(kDwThreads)
 dwconv_kernel(const T* __restrict__ x, T* __restrict__ out, const float* __restrict__ wgt,
-              const float* __restrict__ bias, pool_t* __restrict__ pool, int H, int W, int C, int Ho, int Wo, int PAD) {
+              const float* __restrict__ bias, pool_t* __restrict__ pool, int H, int W, int C, int Ho, int Wo, int PAD,
+              int act) {
   extern __shared__ unsigned long long spool[];  // [C] Q24
   constexpr int IW = (TW - 1) * S + K;  // input columns a strip touches
   constexpr bool kFast = is_bf16<T>::value;
@@ -88,7 +89,7 @@ dwconv_kernel(const T* __restrict__ x, T* __restrict__ out, const float* __restr
         float f[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          f[e] = silu<kFast>(acc[j][e]);
+          f[e] = apply_act<kFast>(acc[j][e], act);
         }
         if constexpr (kFast) {
           // pool what the consumer will actually read (bf16-rounded values)
@@ -119,7 +120,7 @@ dwconv_kernel(const T* __restrict__ x, T* __restrict__ out, const float* __restr
 
 template <typename T, int K, int S, int TW>
 static cudaError_t dw_launch(const void* x, int n, int h, int w, int c, const float* wgt, const float* bias, void* out,
-                             pool_t* pool, int pad_lo, cudaStream_t s) {
+                             pool_t* pool, int pad_lo, int act, cudaStream_t s) {
   const int PAD = pad_lo < 0 ? (K - 1) / 2 : pad_lo;
   if (PAD > K - 1) return cudaErrorInvalidValue;
   const int Ho = (h - 1) / S + 1, Wo = (w - 1) / S + 1;  // total padding is always k - 1
@@ -132,32 +133,32 @@ static cudaError_t dw_launch(const void* x, int n, int h, int w, int c, const fl
   if (bx > max_bx) bx = max_bx;
   dim3 grid(bx, n);
   dwconv_kernel<T, K, S, TW><<<grid, kDwThreads, c * sizeof(unsigned long long), s>>>(
-      reinterpret_cast<const T*>(x), reinterpret_cast<T*>(out), wgt, bias, pool, h, w, c, Ho, Wo, PAD);
+      reinterpret_cast<const T*>(x), reinterpret_cast<T*>(out), wgt, bias, pool, h, w, c, Ho, Wo, PAD, act);
   count_launch();
   return cudaGetLastError();
 }
 
 template <typename T>
 static cudaError_t dw_dispatch(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                               const float* bias, void* out, pool_t* pool, int pad_lo, cudaStream_t s) {
-  if (k == 3 && stride == 1) return dw_launch<T, 3, 1, 4>(x, n, h, w, c, wgt, bias, out, pool, pad_lo, s);
-  if (k == 3 && stride == 2) return dw_launch<T, 3, 2, 2>(x, n, h, w, c, wgt, bias, out, pool, pad_lo, s);
-  if (k == 5 && stride == 1) return dw_launch<T, 5, 1, 4>(x, n, h, w, c, wgt, bias, out, pool, pad_lo, s);
-  if (k == 5 && stride == 2) return dw_launch<T, 5, 2, 2>(x, n, h, w, c, wgt, bias, out, pool, pad_lo, s);
+                               const float* bias, void* out, pool_t* pool, int pad_lo, int act, cudaStream_t s) {
+  if (k == 3 && stride == 1) return dw_launch<T, 3, 1, 4>(x, n, h, w, c, wgt, bias, out, pool, pad_lo, act, s);
+  if (k == 3 && stride == 2) return dw_launch<T, 3, 2, 2>(x, n, h, w, c, wgt, bias, out, pool, pad_lo, act, s);
+  if (k == 5 && stride == 1) return dw_launch<T, 5, 1, 4>(x, n, h, w, c, wgt, bias, out, pool, pad_lo, act, s);
+  if (k == 5 && stride == 2) return dw_launch<T, 5, 2, 2>(x, n, h, w, c, wgt, bias, out, pool, pad_lo, act, s);
   return cudaErrorInvalidValue;
 }
 
 cudaError_t launch_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                          const float* bias, void* out, pool_t* pool, int dtype, cudaStream_t s, int pad_lo) {
+                          const float* bias, void* out, pool_t* pool, int dtype, cudaStream_t s, int pad_lo, int act) {
   if (n <= 0) return cudaSuccess;
   if (c % 8 != 0 || c > 6144) return cudaErrorInvalidValue;
   if (dtype == kBF16) {
     DwPlan plan;  // bf16: TMA-staged kernel (dwconv_tma.cu) whenever the shape allows it
-    if (plan_dwconv_tma(plan, x, n, h, w, c, k, stride, wgt, bias, out, pool, pad_lo) == 0)
+    if (plan_dwconv_tma(plan, x, n, h, w, c, k, stride, wgt, bias, out, pool, pad_lo, act) == 0)
       return launch_dwconv_tma(plan, s);
-    return dw_dispatch<bf16>(x, n, h, w, c, k, stride, wgt, bias, out, pool, pad_lo, s);
+    return dw_dispatch<bf16>(x, n, h, w, c, k, stride, wgt, bias, out, pool, pad_lo, act, s);
   }
-  return dw_dispatch<float>(x, n, h, w, c, k, stride, wgt, bias, out, pool, pad_lo, s);
+  return dw_dispatch<float>(x, n, h, w, c, k, stride, wgt, bias, out, pool, pad_lo, act, s);
 }
 
 }  // namespace b200df

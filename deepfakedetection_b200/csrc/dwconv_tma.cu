@@ -72,7 +72,9 @@ struct DwTile { int cb, tx, ty, ng; };
 // (Three CTAs per SM for the 3x3 single-column variants -- 80 registers, <= 74 KB plans -- measured slower.)
 // PL: zero rows/columns before the image.  (K-1)/2 everywhere except the TF-"same" 3x3 stride-2 layers of the
 // efficientnet_pytorch layout (pad (0, 1): PL = 0, the box then starts on the even column 2*ox itself).
-template <int K, int S, int TH, int NC, int PL = (K - 1) / 2>
+// ACT: activation after the folded-BN bias (common.cuh Act): SiLU (EfficientNet), GELU (EfficientFormerV2 `mlp.mid`),
+// none (EfficientFormerV2 `stride_conv` / `v_local` / `q.local`, FasterViT `global_tokenizer.pos_embed`).
+template <int K, int S, int TH, int NC, int PL = (K - 1) / 2, int ACT = kActSiLU>
 __global__ void __launch_bounds__(256, 2)
 dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -163,7 +165,8 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
   f32x2 w[K * K];
   f32x2 bias2 = 0ull;
   auto load_weights = [&]() {
-    const f32x2 half2 = pack2(0.5f, 0.5f);
+    constexpr float kPre = ACT == kActNone ? 1.0f : 0.5f;   // SiLU / GELU work on h = x/2
+    const f32x2 half2 = pack2(kPre, kPre);
 #pragma unroll
     for (int i = 0; i < K * K; ++i) {
       float2 v = c_ok ? __ldg(reinterpret_cast<const float2*>(p.wgt + (size_t)i * p.C + c0)) : make_float2(0.f, 0.f);
@@ -248,7 +251,18 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmap, const DwTmaParams p)
           for (int j = 0; j < TH; ++j) {
             float h0, h1;
             unpack2(acc[q][j], h0, h1);
-            const f32x2 f = fma2(acc[q][j], pack2(tanh_fast(h0), tanh_fast(h1)), acc[q][j]);
+            f32x2 f;
+            if constexpr (ACT == kActSiLU) {
+              f = fma2(acc[q][j], pack2(tanh_fast(h0), tanh_fast(h1)), acc[q][j]);
+            } else if constexpr (ACT == kActGELU) {  // h + h tanh(h (c1 + c3 h^2)), common.cuh gelu_fast
+              const f32x2 u = mul2(acc[q][j], fma2(mul2(acc[q][j], acc[q][j]), pack2(0.2854191951f, 0.2854191951f),
+                                                   pack2(1.5957691216f, 1.5957691216f)));
+              float u0, u1;
+              unpack2(u, u0, u1);
+              f = fma2(acc[q][j], pack2(tanh_fast(u0), tanh_fast(u1)), acc[q][j]);
+            } else {
+              f = acc[q][j];
+            }
             float f0, f1;
             unpack2(f, f0, f1);
             if (rows_full || oy0 + j < p.Ho) {
@@ -333,14 +347,13 @@ int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsign
 
 namespace {
 
-template <int K, int S, int TH, int NC, int PL = (K - 1) / 2>
+template <int K, int S, int TH, int NC, int PL = (K - 1) / 2, int ACT = kActSiLU>
 cudaError_t dw_tma_launch(const DwPlan& pl, cudaStream_t s) {
-  auto kern = dwconv_tma_kernel<K, S, TH, NC, PL>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  auto kern = dwconv_tma_kernel<K, S, TH, NC, PL, ACT>;
+  static PerDeviceOnce once;
+  if (once.need()) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
-    attr_done = true;
   }
   count_launch();
   return launch_pdl(kern, dim3(pl.grid), dim3(pl.block), pl.smem, s, *reinterpret_cast<const CUtensorMap*>(pl.tmap), pl.p);
@@ -381,20 +394,10 @@ static size_t dw_smem_limit() {  // B200DF_DW_SMEM_KB: sweep aid (e.g. 74 -> pla
 }  // namespace
 
 int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                    const float* bias, void* out, pool_t* pool, int pad_lo) {
-  plan.tc = 0;
-  {  // EXPERIMENT, off by default (B200DF_DW_TC=1): stride-1 layers on the tensor cores (dwconv_tc.cu).
-     // Measured 2x SLOWER than this CUDA-core kernel: every tap re-streams the whole pixel tile from shared
-     // memory into the tensor core (k*k tile reads, ~80 cycles per M128 N16 K16 MMA), see DESIGN.md section 4.
-    static int use_tc = -1;
-    if (use_tc < 0) {
-      const char* e = getenv("B200DF_DW_TC");
-      use_tc = (e && e[0] == '1') ? 1 : 0;
-    }
-    if (use_tc && pad_lo < 0 && plan_dwconv_tc(plan, x, n, h, w, c, k, stride, wgt, bias, out, pool) == 0) return 0;
-    plan.tc = 0;
-  }
+                    const float* bias, void* out, pool_t* pool, int pad_lo, int act) {
   if (n <= 0 || c % 8 || (k != 3 && k != 5) || (stride != 1 && stride != 2)) return -1;
+  if (act != kActSiLU && !((act == kActNone || act == kActGELU) && k == 3 && pad_lo < 0)) return -1;
+  plan.act = act;
   if (stride == 2 && (w & 1)) return -1;
   const int pad = pad_lo < 0 ? (k - 1) / 2 : pad_lo;
   // an explicit pad-before other than (k-1)/2 exists only for the TF-"same" 3x3 stride-2 layers: pad (0, 1)
@@ -521,7 +524,16 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
 }
 
 cudaError_t launch_dwconv_tma(const DwPlan& pl, cudaStream_t s) {
-  if (pl.tc) return launch_dwconv_tc(pl, s);
+  if (pl.act != kActSiLU) {  // 3x3 only (plan_dwconv_tma refuses the rest)
+#define DW_CASE_ACT(S_, TH_, NC_)                                                                                       \
+  if (pl.k == 3 && pl.stride == S_ && pl.th == TH_ && pl.nc == NC_)                                                      \
+    return pl.act == kActGELU ? dw_tma_launch<3, S_, TH_, NC_, 1, kActGELU>(pl, s)                                      \
+                              : dw_tma_launch<3, S_, TH_, NC_, 1, kActNone>(pl, s)
+    DW_CASE_ACT(1, 8, 1); DW_CASE_ACT(1, 7, 1); DW_CASE_ACT(2, 8, 1); DW_CASE_ACT(2, 7, 1);
+    DW_CASE_ACT(1, 8, 2); DW_CASE_ACT(1, 7, 2);
+#undef DW_CASE_ACT
+    return cudaErrorInvalidValue;
+  }
   if (pl.k == 3 && pl.stride == 2 && pl.nc == 1 && pl.pad_lo == 0)
     return pl.th == 8 ? dw_tma_launch<3, 2, 8, 1, 0>(pl, s) : dw_tma_launch<3, 2, 7, 1, 0>(pl, s);
 #define DW_CASE(K_, S_, TH_, NC_) \

@@ -75,6 +75,14 @@ static int require_sm100(int device) {
   return B200DF_OK;
 }
 
+// layer programs (nets.inc, included further down)
+namespace {
+bool is_net_arch(int arch);
+void describe_net(b200df_engine* e);
+int finalize_net(b200df_engine* h, int precision);
+NetWs layout_net_workspace(const b200df_engine* h, int n);
+}  // namespace
+
 // ---- EfficientNet-B0 description (timm layout) ---------------------------
 static void add_slot(b200df_engine* e, const std::string& name, size_t numel) {
   TensorSlot s;
@@ -196,7 +204,7 @@ static void describe_effnet_b3(b200df_engine* e) {
 extern "C" int b200df_create(int arch, int num_classes, int device, b200df_handle* out) {
   if (!out) return fail(B200DF_E_INVALID, "out is NULL");
   *out = nullptr;
-  if (arch != B200DF_ARCH_EFFICIENTNET_B0 && arch != B200DF_ARCH_EFFICIENTNET_B3)
+  if (arch != B200DF_ARCH_EFFICIENTNET_B0 && arch != B200DF_ARCH_EFFICIENTNET_B3 && !is_net_arch(arch))
     return fail(B200DF_E_INVALID, "unknown arch id %d", arch);
   if (num_classes < 1 || num_classes > 4096) return fail(B200DF_E_INVALID, "num_classes %d out of range", num_classes);
   // No device is needed to describe a model (tests list the expected tensors on CPU boxes);
@@ -205,7 +213,8 @@ extern "C" int b200df_create(int arch, int num_classes, int device, b200df_handl
   e->arch = arch;
   e->num_classes = num_classes;
   e->device = device;
-  if (arch == B200DF_ARCH_EFFICIENTNET_B3) describe_effnet_b3(e);
+  if (is_net_arch(arch)) describe_net(e);
+  else if (arch == B200DF_ARCH_EFFICIENTNET_B3) describe_effnet_b3(e);
   else describe_effnet_b0(e);
   *out = e;
   return B200DF_OK;
@@ -216,8 +225,13 @@ static void free_device(b200df_engine* e) {
     cudaFree(e->arena);
     e->arena = nullptr;
   }
+  if (e->head_scratch) {
+    cudaFree(e->head_scratch);
+    e->head_scratch = nullptr;
+    e->head_scratch_cap = 0;
+  }
   e->bdev.clear();
-  e->plan = Plan();
+  e->plans.clear();
   e->precision = -1;
 }
 
@@ -246,6 +260,11 @@ extern "C" int b200df_tensor_info(b200df_handle h, int index, const char** name,
 }
 
 extern "C" int b200df_feature_shape(b200df_handle h, int* channels, int* side) {
+  if (h && h->net) {
+    if (channels) *channels = h->net->feat_c;
+    if (side) *side = h->net->feat_side;
+    return B200DF_OK;
+  }
   if (!h || h->blocks.empty()) return fail(B200DF_E_INVALID, "NULL handle");
   if (channels) *channels = h->head_c;
   if (side) *side = h->blocks.back().hout;
@@ -369,6 +388,16 @@ extern "C" int b200df_finalize(b200df_handle h, int precision) {
   if (rc != B200DF_OK) return rc;
   CU_OK(cudaSetDevice(h->device));
   free_device(h);
+  h->gemm_impl = precision == B200DF_PREC_BF16 ? 0 : 1;
+  if (const char* env = getenv("B200DF_GEMM")) {  // debugging aid: force the SIMT GEMM / conv on the bf16 path
+    if (strcmp(env, "simt") == 0) h->gemm_impl = 1;
+  }
+  h->dw_impl = 0;
+  if (h->net) {
+    rc = finalize_net(h, precision);
+    if (rc == B200DF_OK) h->precision = precision;
+    return rc;
+  }
 
   Packer pk;
   std::vector<float> sc, sh, tmp;
@@ -455,11 +484,6 @@ extern "C" int b200df_finalize(b200df_handle h, int precision) {
   h->fc_w = F(fw);
   h->fc_b = F(fb);
   h->precision = precision;
-  h->gemm_impl = precision == B200DF_PREC_BF16 ? 0 : 1;
-  if (const char* env = getenv("B200DF_GEMM")) {  // debugging aid: force the SIMT GEMM on the bf16 path
-    if (strcmp(env, "simt") == 0) h->gemm_impl = 1;
-  }
-  h->dw_impl = 0;
   if (const char* env = getenv("B200DF_DW")) {  // debugging aid: force the plain (non-TMA) depthwise kernel
     if (strcmp(env, "plain") == 0) h->dw_impl = 1;
   }
@@ -498,7 +522,7 @@ extern "C" int b200df_workspace_bytes(b200df_handle h, int n, int mode, size_t* 
   (void)mode;
   if (!h || !bytes || n < 0) return fail(B200DF_E_INVALID, "bad argument");
   if (h->precision < 0) return fail(B200DF_E_STATE, "b200df_finalize has not been called");
-  *bytes = layout_workspace(h, n > 0 ? n : 1).total;
+  *bytes = h->net ? layout_net_workspace(h, n > 0 ? n : 1).total : layout_workspace(h, n > 0 ? n : 1).total;
   return B200DF_OK;
 }
 
@@ -537,15 +561,43 @@ struct GemmCall {  // one pointwise conv in schedule order
   void* out;
 };
 
-int run_gemm(b200df_engine* h, const GemmCall& g, int index, cudaStream_t s) {
+// The plan (tensor maps, depthwise tile plans) of this (n, workspace) pair: the engine keeps a few of them, so a
+// loader that alternates full batches / a ragged tail / val and test splits does not re-encode ~80 tensor maps
+// per switch.  Least recently used is evicted.
+Plan& plan_for(b200df_engine* h, int n, void* ws) {
+  constexpr size_t kMaxPlans = 6;
+  ++h->plan_clock;
+  for (auto& p : h->plans)
+    if (p.n == n && p.ws == ws) {
+      p.stamp = h->plan_clock;
+      return p;
+    }
+  if (h->plans.size() < kMaxPlans) {
+    h->plans.reserve(kMaxPlans);   // references handed out earlier stay valid
+    h->plans.emplace_back();
+  } else {
+    size_t lru = 0;
+    for (size_t i = 1; i < h->plans.size(); ++i)
+      if (h->plans[i].stamp < h->plans[lru].stamp) lru = i;
+    std::swap(h->plans[lru], h->plans.back());
+    h->plans.back() = Plan();
+  }
+  Plan& p = h->plans.back();
+  p.n = n;
+  p.ws = ws;
+  p.stamp = h->plan_clock;
+  return p;
+}
+
+int run_gemm(b200df_engine* h, Plan& plan, const GemmCall& g, int index, cudaStream_t s) {
   const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
   if (h->gemm_impl == 1) {
     CU_OK(launch_pwconv_simt(g.x, g.m, g.L->cin, g.L->cout, g.L->w, g.L->bias, g.gate, g.rows_per_img, g.residual,
                              g.act, g.out, dt, s));
     return B200DF_OK;
   }
-  if ((int)h->plan.gemms.size() <= index) h->plan.gemms.resize(index + 1);
-  TcGemmArgs& a = h->plan.gemms[index];
+  if ((int)plan.gemms.size() <= index) plan.gemms.resize(index + 1);
+  TcGemmArgs& a = plan.gemms[index];
   if (a.out != g.out || a.m != g.m) {  // (re)encode tensor maps for this (n, workspace)
     memset(&a, 0, sizeof(a));
     const int rpi = g.gate ? g.rows_per_img : 0;
@@ -572,15 +624,19 @@ int run_gemm(b200df_engine* h, const GemmCall& g, int index, cudaStream_t s) {
 
 enum InputKind { kInF32NCHW = 0, kInU8HWC = 1 };
 
+// dense 3x3 conv of a layer program: tcgen05 implicit GEMM when the shape allows it (bf16), CUDA-core GEMM otherwise
+int run_conv3(b200df_engine* h, Plan& plan, int index, const void* x, int n, int hin, int cin, int cout, int stride,
+              const void* w, const float* bias, const void* residual, int act, void* out, int dt, cudaStream_t s) {
+  (void)plan; (void)index;
+  CU_OK(launch_conv3x3_simt(x, n, hin, hin, cin, cout, stride, w, bias, residual, act, out, dt, s));
+  return B200DF_OK;
+}
+
 // Runs stem -> 16 MBConv blocks -> conv_head.  Leaves A (raw conv_head output, NHWC) in ws.a.
 int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in_sc, const float* in_sh, int n,
               uint8_t* ws, const Workspace& W, cudaStream_t s) {
   const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
-  if (h->plan.n != n || h->plan.ws != ws) {
-    h->plan = Plan();
-    h->plan.n = n;
-    h->plan.ws = ws;
-  }
+  Plan& plan = plan_for(h, n, ws);
   pool_t* pool = reinterpret_cast<pool_t*>(ws + W.pool);
   float* gate = reinterpret_cast<float*>(ws + W.gate);
   CU_OK(cudaMemsetAsync(pool, 0, h->pool_floats_per_img * n * sizeof(pool_t), s));
@@ -610,7 +666,7 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
       pr = prof_begin(h, s, "expand", li, (double)m_in * (b.cin + b.mid) * es + (double)b.mid * b.cin * es,
                       2.0 * m_in * b.cin * b.mid);
       GemmCall g{&d.expand, cur, m_in, nullptr, 1, nullptr, 1, ws + W.e};
-      int rc = run_gemm(h, g, gi++, s);
+      int rc = run_gemm(h, plan, g, gi++, s);
       if (rc) return rc;
       prof_end(pr, s);
       dw_in = ws + W.e;
@@ -621,8 +677,8 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
     {
       bool done = false;
       if (dt == kBF16 && h->dw_impl == 0) {
-        if (h->plan.dws.size() != h->blocks.size()) h->plan.dws.assign(h->blocks.size(), DwPlan());
-        DwPlan& dp = h->plan.dws[i];
+        if (plan.dws.size() != h->blocks.size()) plan.dws.assign(h->blocks.size(), DwPlan());
+        DwPlan& dp = plan.dws[i];
         if (dp.x != dw_in || dp.p.n != n || dp.p.pool != pool_b) {
           dp.x = nullptr;
           if (plan_dwconv_tma(dp, dw_in, n, b.hin, b.hin, b.mid, b.k, b.stride, d.dw_w, d.dw_b, ws + W.d, pool_b,
@@ -647,7 +703,7 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
                     (double)m_out * (b.mid + b.cout * (b.skip ? 2 : 1)) * es + (double)b.mid * b.cout * es,
                     2.0 * m_out * b.mid * b.cout);
     GemmCall g{&d.project, ws + W.d, m_out, gate_b, b.hout * b.hout, b.skip ? cur : nullptr, 0, nxt};
-    int rc = run_gemm(h, g, gi++, s);
+    int rc = run_gemm(h, plan, g, gi++, s);
     if (rc) return rc;
     prof_end(pr, s);
     std::swap(cur, nxt);
@@ -657,22 +713,41 @@ int run_trunk(b200df_engine* h, const void* images, int in_kind, const float* in
   pr = prof_begin(h, s, "conv_head", -1, (double)n * hw * (cin_head + h->head_c) * es + (double)h->head_c * cin_head * es,
                   2.0 * n * hw * cin_head * h->head_c);
   GemmCall g{&h->head, cur, (long long)n * hw, nullptr, 1, nullptr, 0, ws + W.a};
-  int rc = run_gemm(h, g, gi++, s);
+  int rc = run_gemm(h, plan, g, gi++, s);
   prof_end(pr, s);
   return rc;
+}
+
+int check_ws(int n, const void* ws, size_t ws_bytes, size_t need) {
+  if (n > 0) {
+    if (!ws || (reinterpret_cast<uintptr_t>(ws) & 1023))
+      return fail(B200DF_E_WORKSPACE, "workspace must be non-NULL and 1024-byte aligned");
+    if (ws_bytes < need)
+      return fail(B200DF_E_WORKSPACE, "workspace too small: %zu < %zu bytes for n=%d", ws_bytes, need, n);
+  }
+  return B200DF_OK;
 }
 
 int check_call(b200df_engine* h, int n, const void* ws, size_t ws_bytes, Workspace* W) {
   if (!h) return fail(B200DF_E_INVALID, "NULL handle");
   if (h->precision < 0) return fail(B200DF_E_STATE, "b200df_finalize has not been called");
   if (n < 0) return fail(B200DF_E_INVALID, "negative batch");
+  if (h->net) return B200DF_OK;   // layer programs lay out their own workspace (check_net_call)
   *W = layout_workspace(h, n > 0 ? n : 1);
-  if (n > 0) {
-    if (!ws || (reinterpret_cast<uintptr_t>(ws) & 1023))
-      return fail(B200DF_E_WORKSPACE, "workspace must be non-NULL and 1024-byte aligned");
-    if (ws_bytes < W->total)
-      return fail(B200DF_E_WORKSPACE, "workspace too small: %zu < %zu bytes for n=%d", ws_bytes, W->total, n);
-  }
+  return check_ws(n, ws, ws_bytes, W->total);
+}
+
+// Explicit Grad-CAM targets are validated on the host (pytorch-grad-cam's ClassifierOutputTarget raises IndexError on a
+// class the model does not have, /root/reference/web_ui.py:278): one small D2H copy + a stream synchronize, only on
+// the CAM entry points and only when the caller passes targets.
+int check_targets(const int32_t* target_cls, int n, int num_classes, cudaStream_t s) {
+  if (!target_cls || n <= 0) return B200DF_OK;
+  std::vector<int32_t> t(n);
+  CU_OK(cudaMemcpyAsync(t.data(), target_cls, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  CU_OK(cudaStreamSynchronize(s));
+  for (int i = 0; i < n; ++i)
+    if (t[i] < 0 || t[i] >= num_classes)
+      return fail(B200DF_E_INVALID, "Grad-CAM target class %d (image %d) out of range [0, %d)", t[i], i, num_classes);
   return B200DF_OK;
 }
 
@@ -693,6 +768,15 @@ int run_head(b200df_engine* h, int n, uint8_t* ws, const Workspace& W, float* lo
 
 }  // namespace
 
+#include "nets.inc"
+
+namespace {
+int check_net_call(b200df_engine* h, int n, const void* ws, size_t ws_bytes, NetWs* W) {
+  *W = layout_net_workspace(h, n > 0 ? n : 1);
+  return check_ws(n, ws, ws_bytes, W->total);
+}
+}  // namespace
+
 extern "C" int b200df_forward(b200df_handle h, const float* images, int n, float* logits, void* workspace,
                               size_t workspace_bytes, void* stream) {
   Workspace W;
@@ -701,6 +785,12 @@ extern "C" int b200df_forward(b200df_handle h, const float* images, int n, float
   if (!images || !logits) return fail(B200DF_E_INVALID, "NULL images/logits");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  if (h->net) {
+    NetWs NW;
+    rc = check_net_call(h, n, workspace, workspace_bytes, &NW);
+    if (rc) return rc;
+    return run_net(h, images, kInF32NCHW, nullptr, nullptr, n, ws, NW, logits, s);
+  }
   rc = run_trunk(h, images, kInF32NCHW, nullptr, nullptr, n, ws, W, s);
   if (rc) return rc;
   return run_head(h, n, ws, W, logits, s);
@@ -721,6 +811,12 @@ extern "C" int b200df_forward_u8(b200df_handle h, const uint8_t* images_hwc, int
   }
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  if (h->net) {
+    NetWs NW;
+    rc = check_net_call(h, n, workspace, workspace_bytes, &NW);
+    if (rc) return rc;
+    return run_net(h, images_hwc, kInU8HWC, sc, sh, n, ws, NW, logits, s);
+  }
   rc = run_trunk(h, images_hwc, kInU8HWC, sc, sh, n, ws, W, s);
   if (rc) return rc;
   return run_head(h, n, ws, W, logits, s);
@@ -736,6 +832,32 @@ extern "C" int b200df_forward_cam(b200df_handle h, const float* images, int n, c
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
   const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
+  rc = check_targets(target_cls, n, h->num_classes, s);
+  if (rc) return rc;
+  if (h->net) {
+    Net* net = h->net.get();
+    if (!net->wcam)
+      return fail(B200DF_E_STATE, "Grad-CAM for this architecture needs a backward pass through its transformer blocks "
+                                  "(the reference's target rule picks a conv in front of them, web_ui.py:96-105): not built");
+    NetWs NW;
+    rc = check_net_call(h, n, workspace, workspace_bytes, &NW);
+    if (rc) return rc;
+    float* lg = logits ? logits : reinterpret_cast<float*>(ws + NW.logits);
+    rc = run_net(h, images, kInF32NCHW, nullptr, nullptr, n, ws, NW, lg, s);
+    if (rc) return rc;
+    const int fs = net->feat_side, fhw = fs * fs;
+    float* low = cam_lowres ? cam_lowres : reinterpret_cast<float*>(ws + NW.cam_low);
+    ProfRec* pr = prof_begin(h, s, "cam", -1, (double)n * fhw * net->feat_c * (dt == kBF16 ? 2.0 : 4.0) + (double)n * fhw * 4,
+                             2.0 * n * fhw * net->feat_c);
+    CU_OK(launch_cam_linear(ws + NW.off[net->a_buf], n, fhw, net->feat_c, net->wcam, h->num_classes, target_cls, lg, low, dt, s));
+    prof_end(pr, s);
+    if (cam) {
+      pr = prof_begin(h, s, "cam_upsample", -1, (double)n * (fhw + (double)h->img * h->img) * 4, 8.0 * n * h->img * h->img);
+      CU_OK(launch_cam_upsample(low, n, fs, h->img, cam, s));
+      prof_end(pr, s);
+    }
+    return B200DF_OK;
+  }
   const int side = h->blocks.back().hout, hw = side * side;
   rc = run_trunk(h, images, kInF32NCHW, nullptr, nullptr, n, ws, W, s);
   if (rc) return rc;
@@ -756,8 +878,11 @@ extern "C" int b200df_forward_cam(b200df_handle h, const float* images, int n, c
   return B200DF_OK;
 }
 
-extern "C" int b200df_trunk(b200df_handle h, const float* images, int n, float* a_nchw, void* workspace,
-                            size_t workspace_bytes, void* stream) {
+// aux: float32 [n, num_classes] (nullable).  For the affine-head architectures (EfficientFormerV2: everything after
+// the Grad-CAM activation A is affine, but part of it -- the block's residual input -- is not a function of A) it
+// receives logits - lin(A), so that head_ex(A, aux) reproduces the logits; the MBConv engines write zeros.
+static int trunk_impl(b200df_handle h, const float* images, int n, float* a_nchw, float* aux, void* workspace,
+                      size_t workspace_bytes, void* stream) {
   Workspace W;
   int rc = check_call(h, n, workspace, workspace_bytes, &W);
   if (rc || n == 0) return rc;
@@ -765,36 +890,66 @@ extern "C" int b200df_trunk(b200df_handle h, const float* images, int n, float* 
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
   const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
+  if (h->net) {
+    Net* net = h->net.get();
+    if (!net->wcam) return fail(B200DF_E_STATE, "the split trunk/head (Grad-CAM hook) path is not built for this architecture");
+    if (!aux) return fail(B200DF_E_INVALID, "this architecture's split head needs the aux output (b200df_trunk_ex)");
+    NetWs NW;
+    rc = check_net_call(h, n, workspace, workspace_bytes, &NW);
+    if (rc) return rc;
+    float* lg = reinterpret_cast<float*>(ws + NW.logits);
+    rc = run_net(h, images, kInF32NCHW, nullptr, nullptr, n, ws, NW, lg, s);
+    if (rc) return rc;
+    const int fhw = net->feat_side * net->feat_side;
+    CU_OK(launch_nhwc_to_nchw_f32(ws + NW.off[net->a_buf], n, fhw, net->feat_c, a_nchw, dt, s));
+    CU_OK(launch_lin_head(a_nchw, lg, n, fhw, net->feat_c, net->wcam, h->num_classes, 1, aux, s));
+    return B200DF_OK;
+  }
   const int hw = h->blocks.back().hout * h->blocks.back().hout;
   rc = run_trunk(h, images, kInF32NCHW, nullptr, nullptr, n, ws, W, s);
   if (rc) return rc;
   CU_OK(launch_nhwc_to_nchw_f32(ws + W.a, n, hw, h->head_c, a_nchw, dt, s));
+  if (aux) CU_OK(cudaMemsetAsync(aux, 0, (size_t)n * h->num_classes * sizeof(float), s));
   return B200DF_OK;
 }
 
-// Scratch for the split head: pooled [n,1280] lives in a small per-engine cache grown on demand
-// (outside stream capture), so head()/head_backward() need no caller workspace.
+extern "C" int b200df_trunk(b200df_handle h, const float* images, int n, float* a_nchw, void* workspace,
+                            size_t workspace_bytes, void* stream) {
+  return trunk_impl(h, images, n, a_nchw, nullptr, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200df_trunk_ex(b200df_handle h, const float* images, int n, float* a_nchw, float* aux, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+  return trunk_impl(h, images, n, a_nchw, aux, workspace, workspace_bytes, stream);
+}
+
+// Scratch for the split head: pooled [n, head_c] lives in a per-ENGINE buffer on the engine's device, grown on
+// demand (outside stream capture), so head()/head_backward() need no caller workspace.
 static int head_scratch(b200df_engine* h, int n, float** out) {
-  static thread_local float* buf = nullptr;
-  static thread_local size_t cap = 0;
-  size_t need = (size_t)n * h->head_c * sizeof(float);
-  if (need > cap) {
-    if (buf) cudaFree(buf);
-    buf = nullptr;
-    cap = 0;
-    CU_OK(cudaMalloc(&buf, need));
-    cap = need;
+  const size_t need = (size_t)n * h->head_c * sizeof(float);
+  if (need > h->head_scratch_cap) {
+    if (h->head_scratch) CU_OK(cudaFree(h->head_scratch));
+    h->head_scratch = nullptr;
+    h->head_scratch_cap = 0;
+    CU_OK(cudaMalloc(&h->head_scratch, need));
+    h->head_scratch_cap = need;
   }
-  (void)h;
-  *out = buf;
+  *out = h->head_scratch;
   return B200DF_OK;
 }
 
-extern "C" int b200df_head(b200df_handle h, const float* a_nchw, int n, float* logits, void* stream) {
+static int head_impl(b200df_handle h, const float* a_nchw, const float* aux, int n, float* logits, void* stream) {
   if (!h || h->precision < 0) return fail(B200DF_E_STATE, "engine not finalized");
   if (n <= 0) return n == 0 ? B200DF_OK : fail(B200DF_E_INVALID, "negative batch");
   if (!a_nchw || !logits) return fail(B200DF_E_INVALID, "NULL argument");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (h->net) {
+    Net* net = h->net.get();
+    if (!net->wcam) return fail(B200DF_E_STATE, "the split trunk/head (Grad-CAM hook) path is not built for this architecture");
+    if (!aux) return fail(B200DF_E_INVALID, "this architecture's split head needs the aux input (b200df_head_ex)");
+    CU_OK(launch_lin_head(a_nchw, aux, n, net->feat_side * net->feat_side, net->feat_c, net->wcam, h->num_classes, 0, logits, s));
+    return B200DF_OK;
+  }
   const int hw = h->blocks.back().hout * h->blocks.back().hout;
   float* pooled = nullptr;
   int rc = head_scratch(h, n, &pooled);
@@ -804,12 +959,27 @@ extern "C" int b200df_head(b200df_handle h, const float* a_nchw, int n, float* l
   return B200DF_OK;
 }
 
+extern "C" int b200df_head(b200df_handle h, const float* a_nchw, int n, float* logits, void* stream) {
+  return head_impl(h, a_nchw, nullptr, n, logits, stream);
+}
+
+extern "C" int b200df_head_ex(b200df_handle h, const float* a_nchw, const float* aux, int n, float* logits, void* stream) {
+  return head_impl(h, a_nchw, aux, n, logits, stream);
+}
+
 extern "C" int b200df_head_backward(b200df_handle h, const float* a_nchw, const float* grad_logits, int n,
                                     float* grad_a_nchw, void* stream) {
   if (!h || h->precision < 0) return fail(B200DF_E_STATE, "engine not finalized");
   if (n <= 0) return n == 0 ? B200DF_OK : fail(B200DF_E_INVALID, "negative batch");
   if (!a_nchw || !grad_logits || !grad_a_nchw) return fail(B200DF_E_INVALID, "NULL argument");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (h->net) {
+    Net* net = h->net.get();
+    if (!net->wcam) return fail(B200DF_E_STATE, "the split trunk/head (Grad-CAM hook) path is not built for this architecture");
+    CU_OK(launch_lin_head_backward(grad_logits, n, net->feat_side * net->feat_side, net->feat_c, net->wcam, h->num_classes,
+                                   grad_a_nchw, s));
+    return B200DF_OK;
+  }
   const int hw = h->blocks.back().hout * h->blocks.back().hout;
   CU_OK(launch_head_backward(a_nchw, grad_logits, n, hw, h->head_c, h->head_scale, h->head_shift, h->fc_w, h->num_classes,
                              grad_a_nchw, s));
@@ -859,6 +1029,27 @@ extern "C" int b200df_auc_counts(const float* pos_scores, int n_pos, const float
   if (n_pos < 0 || n_neg < 0 || !less_equal) return fail(B200DF_E_INVALID, "bad argument");
   CU_OK(launch_auc_count(pos_scores, n_pos, neg_scores_sorted, n_neg, reinterpret_cast<unsigned long long*>(less_equal),
                          reinterpret_cast<cudaStream_t>(stream)));
+  return B200DF_OK;
+}
+
+// ---- debug checkpoints of the layer programs (tools/layer_diff.py, tests) ---------------------------------------
+extern "C" int b200df_debug_num_marks(b200df_handle h) { return (h && h->net) ? (int)h->net->marks.size() : 0; }
+
+extern "C" int b200df_debug_mark(b200df_handle h, int index, int n, const char** name, int* op, int* seqs_rows_c,
+                                 size_t* ws_offset) {
+  if (!h || !h->net || index < 0 || index >= (int)h->net->marks.size()) return fail(B200DF_E_INVALID, "mark index out of range");
+  if (h->precision < 0) return fail(B200DF_E_STATE, "b200df_finalize has not been called");
+  const NetMark& m = h->net->marks[index];
+  if (name) *name = m.name.c_str();
+  if (op) *op = m.op;
+  if (seqs_rows_c) { seqs_rows_c[0] = m.seq_rows; seqs_rows_c[1] = m.row_off; seqs_rows_c[2] = m.rows; seqs_rows_c[3] = m.c; }
+  if (ws_offset) *ws_offset = layout_net_workspace(h, n > 0 ? n : 1).off[m.buf];
+  return B200DF_OK;
+}
+
+extern "C" int b200df_debug_stop_after(b200df_handle h, int op) {
+  if (!h || !h->net) return fail(B200DF_E_INVALID, "not a layer-program engine");
+  h->net->stop_after = op;
   return B200DF_OK;
 }
 

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <map>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -49,9 +50,10 @@ struct BlockDev {
   size_t pool_off = 0;     // float offset of this block's [n, mid] pool/gate slabs, per image
 };
 
-struct Plan {  // cached tensor maps for one (n, workspace) pair
+struct Plan {  // cached tensor maps for one (n, workspace) pair; the engine keeps a few (LRU)
   int n = -1;
   void* ws = nullptr;
+  unsigned long long stamp = 0;   // last use
   std::vector<TcGemmArgs> gemms;  // in schedule order
   std::vector<DwPlan> dws;        // per block (bf16 path); x == nullptr -> not planned yet
 };
@@ -66,6 +68,38 @@ struct ProfRec {
 
 struct Workspace {
   size_t t0, t1, e, d, a, pool, gate, pooled, logits, cam_low, total;
+};
+
+// ---- layer programs (nets.inc): EfficientFormerV2 / FasterViT ---------------------------------------------------
+enum OpKind { kOpStem = 0, kOpConv3, kOpPw, kOpDw, kOpAttn, kOpLn, kOpUp, kOpWin, kOpCtPool, kOpAddPos, kOpCopyRows, kOpTail };
+
+struct NetOp {
+  int kind = 0;
+  char cls[24] = "";            // profiling class
+  int in = -1, in2 = -1, in3 = -1, out = -1;   // activation buffer ids
+  int i[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  float f[2] = {0.f, 0.f};
+  const void* p[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  PwLayer pw;
+  AttnArgs attn;
+  double bytes = 0, wbytes = 0, flops = 0;     // algorithmic: activations per image, weights per launch, flops per image
+};
+
+struct NetWs { std::vector<size_t> off; size_t logits = 0, cam_low = 0, aux = 0, total = 0; };
+
+// Debug checkpoint: after op `op`, buffer `buf` holds [n, rows, c] = the reference tensor `name` (tools/layer_diff.py)
+struct NetMark { std::string name; int op, buf, rows, c, row_off, seq_rows; };
+
+struct Net {
+  std::vector<NetMark> marks;
+  int stop_after = -1;             // debug: run_net returns after this op (-1 = run everything)
+  std::vector<size_t> buf_elems;   // per image
+  std::vector<int> buf_f32;
+  std::vector<NetOp> ops;
+  int a_buf = -1, resid_buf = -1;  // Grad-CAM activation A (raw output of the reference's target conv) / its residual input
+  int feat_c = 0, feat_side = 0;
+  size_t wcam_off = ~size_t(0);    // arena offset of d logit / d A [num_classes, feat_c] (affine heads only)
+  const float* wcam = nullptr;
 };
 
 }  // namespace b200df
@@ -95,7 +129,11 @@ struct b200df_engine {
   size_t pool_floats_per_img = 0;
   int gemm_impl = 0;  // 0 = tcgen05 (bf16), 1 = SIMT
   int dw_impl = 0;    // 0 = TMA halo kernel (bf16), 1 = plain kernel
-  b200df::Plan plan;
+  std::vector<b200df::Plan> plans;   // a few (n, workspace) plans, least recently used evicted
+  unsigned long long plan_clock = 0;
+  std::unique_ptr<b200df::Net> net;  // layer program (EfficientFormerV2 / FasterViT); null for the MBConv engines
+  float* head_scratch = nullptr;     // pooled [n, head_c] for the split (hook-protocol) head, grown outside captures
+  size_t head_scratch_cap = 0;
   // profiling (off by default; never on inside a timed region)
   bool profile = false;
   std::vector<b200df::ProfRec> prof;   // event pool, reused across passes

@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "act.h"
+
 namespace b200df {
 
 enum DType : int { kBF16 = 0, kFP32 = 1 };
@@ -33,29 +35,45 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a PER-DEVICE attribute: a launcher that opts a kernel into
+// more than 48 KB of dynamic shared memory must do so once per (kernel instantiation, device), not once per process.
+struct PerDeviceOnce {
+  bool done[64] = {};
+  bool need() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64) return true;
+    if (done[d]) return false;
+    done[d] = true;
+    return true;
+  }
+};
+
 // error plumbing: launchers return cudaError_t of the launch (cudaGetLastError()).
 // oc: stem channels (32 | 40).  pad: zero rows/columns BEFORE the image (1 symmetric, 0 = TF-"same" (0, 1)).
+// act: common.cuh Act (1 SiLU | 2 GELU | 3 ReLU) after the folded bias.  oc: 32 | 40 | 16 (EfficientFormerV2) | 64 (FasterViT).
 cudaError_t launch_stem(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias,
-                        void* out, int dtype, cudaStream_t s, int oc = 32, int pad = 1);
+                        void* out, int dtype, cudaStream_t s, int oc = 32, int pad = 1, int act = 1);
 
 // u8 HWC input, fused ToTensor(/255)+Normalize: in_scale[c] = 1/(255*std[c]), in_shift[c] = -mean[c]/std[c]
 cudaError_t launch_stem_u8(const uint8_t* x_hwc, int n, int h, int w, const float* wgt, const float* bias,
                            float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, void* out,
-                           int dtype, cudaStream_t s, int oc = 32, int pad = 1);
+                           int dtype, cudaStream_t s, int oc = 32, int pad = 1, int act = 1);
 
 // Pooled sums are Q24 fixed-point int64 (common.cuh: pool_t), accumulated with integer atomics.
 typedef long long pool_t;
 // bf16 output only: implicit GEMM on tcgen05 (stem_tc.cu); launch_stem / launch_stem_u8 dispatch to these
+bool stem_tc_supported(int oc, int pad, int act);
 cudaError_t launch_stem_tc(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias, void* out,
-                           cudaStream_t s, int oc = 32, int pad = 1);
+                           cudaStream_t s, int oc = 32, int pad = 1, int act = 1);
 cudaError_t launch_stem_tc_u8(const uint8_t* x_hwc, int n, int h, int w, const float* wgt, const float* bias,
                               float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, void* out,
-                              cudaStream_t s, int oc = 32, int pad = 1);
+                              cudaStream_t s, int oc = 32, int pad = 1, int act = 1);
 
 // pad_lo: zero rows/columns BEFORE the image; -1 = symmetric (k-1)/2.  The pad after is k - 1 - pad_lo, so the
 // output size (h - 1) / stride + 1 does not depend on it (efficientnet_pytorch Conv2dStaticSamePadding).
 cudaError_t launch_dwconv(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                          const float* bias, void* out, pool_t* pool, int dtype, cudaStream_t s, int pad_lo = -1);
+                          const float* bias, void* out, pool_t* pool, int dtype, cudaStream_t s, int pad_lo = -1,
+                          int act = 1);
 
 struct DwTmaParams {
   int C, Ho, Wo;
@@ -75,24 +93,12 @@ struct DwTmaParams {
   pool_t* pool;          // [n, C] Q24 sums or nullptr
 };
 
-// Tensor-core depthwise kernel (dwconv_tc.cu): stride 1, tiles of 8 x 16 output pixels x 64 channels.
-struct DwTcParams {
-  int C, H, W, n;
-  int tiles_x, tiles_y, ncb, stages;
-  uint32_t box_bytes;
-  int stage_stride;
-  const float* wgt;      // [k*k, C] fp32, BN folded (rounded to bf16 when the diagonal tiles are built)
-  const float* bias;     // [C]
-  pool_t* pool;          // [n, C] Q24 sums or nullptr
-};
 
 // A planned depthwise launch: tensor map + tile geometry for one (layer, n, buffers) combination.
 struct DwPlan {
   alignas(64) unsigned char tmap[128];
-  alignas(64) unsigned char tmap_out[128];  // tensor-core kernel only (TMA store)
   DwTmaParams p;
-  DwTcParams q;
-  int tc = 0;            // 1: planned for the tensor-core kernel
+  int act = 1;           // common.cuh Act (SiLU | GELU | none; the last two: 3x3 only)
   int k = 0, stride = 0, th = 0;
   int pad_lo = 1;        // zero rows/columns before the image: (k-1)/2, or 0 for the TF-"same" 3x3 stride-2 layers
   int nc = 1;            // output columns per thread (2: big stride-1 layers, columns x and x+2 share loaded inputs)
@@ -102,12 +108,8 @@ struct DwPlan {
 };
 // bf16 only.  Returns 0 on success (plan filled), <0 if this shape is not supported by the TMA kernel.
 int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                    const float* bias, void* out, pool_t* pool, int pad_lo = -1);
+                    const float* bias, void* out, pool_t* pool, int pad_lo = -1, int act = 1);
 cudaError_t launch_dwconv_tma(const DwPlan& plan, cudaStream_t s);
-// Tensor-core variant (stride 1); plan_dwconv_tma tries it first, launch_dwconv_tma dispatches on plan.tc.
-int plan_dwconv_tc(DwPlan& plan, const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
-                   const float* bias, void* out, pool_t* pool);
-cudaError_t launch_dwconv_tc(const DwPlan& plan, cudaStream_t s);
 // Generic N-d bf16 tensor map (dims/strides innermost first; strides[0] is implicit).  0 on success.
 int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsigned long long* dims,
                         const unsigned long long* strides_bytes, const unsigned* box, int swizzle);
@@ -135,7 +137,7 @@ struct TcGemmArgs {
   const float* gate;  // fp32 [m / rows_per_img, cin] or nullptr
   int rows_per_img;
   const void* residual;  // bf16 [m, cout] or nullptr
-  int act;               // 0 none, 1 SiLU
+  int act;               // common.cuh Act: 0 none, 1 SiLU, 2 GELU, 3 ReLU
   void* out;             // bf16 [m, cout]
 };
 // Encodes a 2D bf16 row-major [rows, cols] tensor map with box [box_rows, 64] and 128B swizzle (weights).
@@ -165,6 +167,51 @@ cudaError_t launch_head_backward(const float* a_nchw, const float* grad_logits, 
                                  float* grad_a, cudaStream_t s);
 cudaError_t launch_softmax_pack(const float* logits, const int64_t* labels, int n, int num_classes, float* packed,
                                 cudaStream_t s);
+
+// ---- dense 3x3 conv (conv3x3.cu: CUDA-core implicit GEMM, any dtype; conv3x3_tc.cu: tcgen05, bf16) ----------------
+// x NHWC [n, h, w, cin]; wgt [cout, 9*cin] with k = (ky*3 + kx)*cin + c in the engine dtype; pad 1; stride 1 | 2.
+cudaError_t launch_conv3x3_simt(const void* x, int n, int h, int w, int cin, int cout, int stride, const void* wgt,
+                                const float* bias, const void* residual, int act, void* out, int dtype,
+                                cudaStream_t s);
+
+// ---- small-sequence attention (attn.cu) ---------------------------------------------------------------------------
+struct AttnArgs {
+  const void* q; const void* k; const void* v;   // engine dtype; token row = pitch elements, head h at off + h*d
+  int q_pitch, k_pitch, v_pitch;
+  int q_off, k_off, v_off;
+  int nseq, nq, nk, dk, dv, heads;
+  float scale;
+  const float* bias;                             // [heads, nq, nk] fp32 or nullptr
+  const float* th1_w; const float* th1_b;        // talking heads: [heads, heads], [heads] (nullptr = none)
+  const float* th2_w; const float* th2_b;
+  const void* vlocal;                            // [nseq*nq, heads*dv] added to the output, or nullptr
+  int act;                                       // common.cuh Act on the output
+  void* out;                                     // [nseq*nq, heads*dv]
+};
+cudaError_t launch_attention(const AttnArgs& a, int dtype, cudaStream_t s);
+
+// ---- transformer glue (vit_ops.cu) ----------------------------------------------------------------------------------
+cudaError_t launch_layernorm(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c,
+                             float eps, int dtype, cudaStream_t s);
+cudaError_t launch_upsample2x_act(const void* x, void* y, int n, int side, int c, int act, int dtype, cudaStream_t s);
+cudaError_t launch_window(const void* src, void* dst, int n, int side, int ws, int ct, int c, const float* pos,
+                          bool reverse, int dtype, cudaStream_t s);
+cudaError_t launch_ct_pool(const void* x, void* ct, int n, int side, int c, int kernel, int stride, int cs, int dtype,
+                           cudaStream_t s);
+cudaError_t launch_add_pos(void* x, long long nseq, int seq_rows, int row_off, int nrows, int c, const float* pos,
+                           int dtype, cudaStream_t s);
+cudaError_t launch_copy_rows(const void* src, void* dst, long long nseq, int src_rows, int src_off, int dst_rows,
+                             int dst_off, int nrows, int c, int dtype, cudaStream_t s);
+cudaError_t launch_pool_affine_fc(const void* a, const void* resid, int n, int hw, int c, const float* a_scale,
+                                  const float* a_shift, const float* n_scale, const float* n_shift, const float* w,
+                                  const float* b, int num_classes, float* logits, int dtype, cudaStream_t s);
+cudaError_t launch_cam_linear(const void* a, int n, int hw, int c, const float* wcam, int num_classes,
+                              const int32_t* target_cls, const float* logits, float* cam_lowres, int dtype,
+                              cudaStream_t s);
+cudaError_t launch_lin_head(const float* a_nchw, const float* aux, int n, int hw, int c, const float* wcam,
+                            int num_classes, int mode, float* out, cudaStream_t s);
+cudaError_t launch_lin_head_backward(const float* grad_logits, int n, int hw, int c, const float* wcam,
+                                     int num_classes, float* grad_a, cudaStream_t s);
 
 // on-device metrics tail (metrics.cu)
 // Grad-CAM overlay (overlay.cu): de-normalise + JET heat map + blend + max-normalise -> uint8 HWC

@@ -10,12 +10,6 @@ namespace b200df {
 
 constexpr int SBM = 64, SBN = 64, SBK = 16, SThreads = 256;
 
-template <typename T> __device__ __forceinline__ float to_f(T v);
-template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
-template <> __device__ __forceinline__ float to_f<bf16>(bf16 v) { return __bfloat162float(v); }
-template <typename T> __device__ __forceinline__ T from_f(float v);
-template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
-template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
 
 template <typename T>
 __global__ void __launch_bounds__(SThreads)
@@ -80,7 +74,7 @@ pwconv_simt_kernel(const T* __restrict__ x, long long M, int K, int N, const T* 
       int nn = n0 + tx * 4 + j;
       if (nn >= N) continue;
       float v = acc[i][j] + bias[nn];
-      if (act == 1) v = is_bf16<T>::value ? silu_fast(v) : silu_acc(v);
+      v = apply_act<is_bf16<T>::value>(v, act);
       if (residual) v += to_f<T>(residual[m * N + nn]);
       out[m * N + nn] = from_f<T>(v);
     }

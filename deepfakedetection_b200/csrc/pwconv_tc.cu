@@ -42,7 +42,7 @@ constexpr int kScalWarps = 8;             // gated kernels: SE-gate scaler warps
 constexpr int kEpiWarps = 8;              // gated kernels: two groups of four (one group per TMEM accumulator)
 constexpr int kEpiWarpsWide = 16;         // ungated kernels (expand, conv_head: wide N, SiLU): two column halves per group
 constexpr int kEpiStageBytes = 32 * 128;  // one staging tile: 32 rows x 64 bf16; TWO per epilogue warp
-constexpr int kMaxBiasFloats = 2304;  // widest layer: EfficientNet-B3 expand 384 -> 2304
+constexpr int kMaxBiasFloats = 3072;  // widest layer: FasterViT-2 level-3 MLP fc1 768 -> 3072 (EfficientNet-B3: 2304)
 
 struct TcParams {
   int m, cin, cout, cout_pad, bn;
@@ -375,6 +375,29 @@ pwconv_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
               for (int j = 0; j < 16; ++j) v[j] = f2_fma(v[j], f2_pack(th[2 * j], th[2 * j + 1]), v[j]);
             }
+            if constexpr (kAct == 2) {  // GELU, tanh form: h + h tanh(h (c1 + c3 h^2)), h = x/2 (common.cuh gelu_fast)
+              float th[32];
+              const f32x2_t c1 = f2_pack(1.5957691216f, 1.5957691216f), c3 = f2_pack(0.2854191951f, 0.2854191951f);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                v[j] = f2_mul(v[j], half2);
+                const f32x2_t u = f2_mul(v[j], f2_fma(f2_mul(v[j], v[j]), c3, c1));
+                float u0, u1;
+                f2_unpack(u, u0, u1);
+                th[2 * j] = tanh_fast(u0);
+                th[2 * j + 1] = tanh_fast(u1);
+              }
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = f2_fma(v[j], f2_pack(th[2 * j], th[2 * j + 1]), v[j]);
+            }
+            if constexpr (kAct == 3) {  // ReLU
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                float a0, a1;
+                f2_unpack(v[j], a0, a1);
+                v[j] = f2_pack(fmaxf(a0, 0.f), fmaxf(a1, 0.f));
+              }
+            }
             if constexpr (kRes) {
 #pragma unroll
               for (int c = 0; c < 4; ++c) {
@@ -636,12 +659,11 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   const int threads = 640;  // gated: 4 + 8 epilogue + 8 scaler warps; ungated: 4 + 16 epilogue warps
 #define TC_LAUNCH(G_, A_, R_)                                                                                  \
   if ((a.gate != nullptr) == G_ && a.act == A_ && res == R_) {                                                 \
-    static bool attr_done = false;                                                                             \
-    if (!attr_done) {                                                                                          \
+    static PerDeviceOnce once;                                                                                 \
+    if (once.need()) {                                                                                         \
       cudaError_t e = cudaFuncSetAttribute(pwconv_tc_kernel<G_, A_, R_>,                                       \
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);           \
       if (e != cudaSuccess) return e;                                                                          \
-      attr_done = true;                                                                                        \
     }                                                                                                          \
     count_launch();                                                                                            \
     return launch_pdl(pwconv_tc_kernel<G_, A_, R_>, dim3(grid), dim3(threads), smem, s, *ta, *tb, *to, p);     \
@@ -654,6 +676,9 @@ cudaError_t launch_pwconv_tc(const TcGemmArgs& a, cudaStream_t s) {
   TC_LAUNCH(false, 1, true)
   TC_LAUNCH(true, 1, false)
   TC_LAUNCH(true, 1, true)
+  TC_LAUNCH(false, 2, false)  // EfficientFormerV2 / FasterViT fc1 (GELU)
+  TC_LAUNCH(false, 2, true)
+  TC_LAUNCH(false, 3, false)
 #undef TC_LAUNCH
   return cudaErrorInvalidValue;
 }

@@ -26,7 +26,7 @@ template <typename TOut, bool kU8, int kStemOC>
 __global__ void __launch_bounds__(kStemThreads)
 stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict__ wgt,
             const float* __restrict__ bias, TOut* __restrict__ out, float sc0, float sc1, float sc2,
-            float sh0, float sh1, float sh2, int pad) {
+            float sh0, float sh1, float sh2, int pad, int act) {
   extern __shared__ float smem[];
   const int Ho = H >> 1, Wo = W >> 1;
   const int PW = W + 2;                  // patch width incl. left/right halo column
@@ -135,8 +135,8 @@ stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict_
       for (int j = 0; j < 4; ++j) {
         float lo, hi;
         asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc0[4 * g + j]));
-        f[2 * j] = silu<kFast>(lo);
-        f[2 * j + 1] = silu<kFast>(hi);
+        f[2 * j] = apply_act<kFast>(lo, act);
+        f[2 * j + 1] = apply_act<kFast>(hi, act);
       }
       store8<TOut>(o0 + 8 * g, f);
     }
@@ -148,8 +148,8 @@ stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict_
         for (int j = 0; j < 4; ++j) {
           float lo, hi;
           asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc1[4 * g + j]));
-          f[2 * j] = silu<kFast>(lo);
-          f[2 * j + 1] = silu<kFast>(hi);
+          f[2 * j] = apply_act<kFast>(lo, act);
+          f[2 * j + 1] = apply_act<kFast>(hi, act);
         }
         store8<TOut>(o0 + kStemOC + 8 * g, f);
       }
@@ -159,7 +159,7 @@ stem_kernel(const void* __restrict__ xin, int H, int W, const float* __restrict_
 
 template <typename TOut, bool kU8, int kStemOC>
 static cudaError_t stem_launch_oc(const void* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
-                                  float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, int pad,
+                                  float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, int pad, int act,
                                   cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   if ((w & 3) || (h & 1) || (w & 1)) return cudaErrorInvalidValue;
@@ -172,7 +172,7 @@ static cudaError_t stem_launch_oc(const void* x, int n, int h, int w, const floa
   }
   dim3 grid((Ho + kStemTR - 1) / kStemTR, n);
   kern<<<grid, kStemThreads, smem, s>>>(x, h, w, wgt, bias, reinterpret_cast<TOut*>(out), sc0, sc1, sc2, sh0, sh1,
-                                        sh2, pad);
+                                        sh2, pad, act);
   count_launch();
   return cudaGetLastError();
 }
@@ -180,10 +180,12 @@ static cudaError_t stem_launch_oc(const void* x, int n, int h, int w, const floa
 template <typename TOut, bool kU8>
 static cudaError_t stem_launch(const void* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
                                float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, int oc, int pad,
-                               cudaStream_t s) {
+                               int act, cudaStream_t s) {
   if (pad != 0 && pad != 1) return cudaErrorInvalidValue;
-  if (oc == 32) return stem_launch_oc<TOut, kU8, 32>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, pad, s);
-  if (oc == 40) return stem_launch_oc<TOut, kU8, 40>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, pad, s);
+#define STEM_OC(OC_) \
+  if (oc == OC_) return stem_launch_oc<TOut, kU8, OC_>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, pad, act, s)
+  STEM_OC(32); STEM_OC(40); STEM_OC(16); STEM_OC(64);  // timm B0 | efficientnet_pytorch B3 | EfficientFormerV2 | FasterViT
+#undef STEM_OC
   return cudaErrorInvalidValue;
 }
 
@@ -198,23 +200,22 @@ static bool stem_force_simt() {
 }
 
 cudaError_t launch_stem(const float* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
-                        int dtype, cudaStream_t s, int oc, int pad) {
+                        int dtype, cudaStream_t s, int oc, int pad, int act) {
   // the tcgen05 stem gathers with 8-byte loads: images not 8-byte aligned take the SIMT kernel
-  if (dtype == kBF16 && ((oc == 32 && pad == 1) || (oc == 40 && pad == 0)) && !stem_force_simt() &&
-      (reinterpret_cast<uintptr_t>(x) & 7) == 0)
-    return launch_stem_tc(x, n, h, w, wgt, bias, out, s, oc, pad);
-  if (dtype == kBF16) return stem_launch<bf16, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, oc, pad, s);
-  return stem_launch<float, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, oc, pad, s);
+  if (dtype == kBF16 && stem_tc_supported(oc, pad, act) && !stem_force_simt() && (reinterpret_cast<uintptr_t>(x) & 7) == 0)
+    return launch_stem_tc(x, n, h, w, wgt, bias, out, s, oc, pad, act);
+  if (dtype == kBF16) return stem_launch<bf16, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, oc, pad, act, s);
+  return stem_launch<float, false>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, oc, pad, act, s);
 }
 
 cudaError_t launch_stem_u8(const uint8_t* x, int n, int h, int w, const float* wgt, const float* bias, float sc0,
                            float sc1, float sc2, float sh0, float sh1, float sh2, void* out, int dtype,
-                           cudaStream_t s, int oc, int pad) {
-  if (dtype == kBF16 && ((oc == 32 && pad == 1) || (oc == 40 && pad == 0)) && !stem_force_simt())
-    return launch_stem_tc_u8(x, n, h, w, wgt, bias, sc0, sc1, sc2, sh0, sh1, sh2, out, s, oc, pad);
+                           cudaStream_t s, int oc, int pad, int act) {
+  if (dtype == kBF16 && stem_tc_supported(oc, pad, act) && !stem_force_simt())
+    return launch_stem_tc_u8(x, n, h, w, wgt, bias, sc0, sc1, sc2, sh0, sh1, sh2, out, s, oc, pad, act);
   if (dtype == kBF16) return stem_launch<bf16, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, oc,
-                                                       pad, s);
-  return stem_launch<float, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, oc, pad, s);
+                                                       pad, act, s);
+  return stem_launch<float, true>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, oc, pad, act, s);
 }
 
 }  // namespace b200df

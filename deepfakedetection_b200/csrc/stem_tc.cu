@@ -28,7 +28,9 @@ constexpr int kStCtasPerSm = 6;
 
 // OC: output channels (32 timm B0 | 40 efficientnet_pytorch B3; the MMA's N is OC rounded up to 16).
 // PAD: zero rows/columns before the image (1 symmetric | 0 = TF-"same" (0, 1), Conv2dStaticSamePadding).
-template <bool kU8, int OC, int PAD>
+// ACT: common.cuh Act applied after the folded bias (SiLU EfficientNet | GELU EfficientFormerV2 `stem.conv1` |
+// ReLU FasterViT `patch_embed.conv_down.0`).
+template <bool kU8, int OC, int PAD, int ACT>
 __global__ void __launch_bounds__(kStT, kStCtasPerSm)
 stem_tc_kernel(const void* __restrict__ xin, int n, int H, int W, const float* __restrict__ wgt,
                const float* __restrict__ bias, bf16* __restrict__ out, float sc0, float sc1, float sc2, float sh0,
@@ -179,17 +181,18 @@ stem_tc_kernel(const void* __restrict__ xin, int n, int H, int W, const float* _
     phase ^= 1;
     tcgen05_fence_after();
     uint32_t r[32];
-    uint32_t r2[16];
+    uint32_t r2[32];
     tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16), r);
-    if constexpr (OC > 32) tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + 32u, r2);
+    if constexpr (OC > 48) tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + 32u, r2);
+    else if constexpr (OC > 32) tmem_ld16(tmem_base + ((uint32_t)(warp * 32) << 16) + 32u, reinterpret_cast<uint32_t(&)[16]>(r2));
     tmem_ld_wait();
     // ---- epilogue: bias + SiLU + bf16, OC * 2 contiguous bytes per pixel ----
     uint4 o[(OC + 7) / 8];
 #pragma unroll
-    for (int ch = 0; ch < 4; ++ch) {
+    for (int ch = 0; ch < (OC < 32 ? OC / 8 : 4); ++ch) {
       float g[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = silu_fast(__uint_as_float(r[ch * 8 + j]) + sbias[ch * 8 + j]);
+      for (int j = 0; j < 8; ++j) g[j] = act_fn<ACT, true>(__uint_as_float(r[ch * 8 + j]) + sbias[ch * 8 + j]);
       o[ch] = pack_bf16x8(g);
     }
     if constexpr (OC > 32) {
@@ -197,7 +200,7 @@ stem_tc_kernel(const void* __restrict__ xin, int n, int H, int W, const float* _
       for (int ch = 4; ch < OC / 8; ++ch) {
         float g[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] = silu_fast(__uint_as_float(r2[(ch - 4) * 8 + j]) + sbias[ch * 8 + j]);
+        for (int j = 0; j < 8; ++j) g[j] = act_fn<ACT, true>(__uint_as_float(r2[(ch - 4) * 8 + j]) + sbias[ch * 8 + j]);
         o[ch] = pack_bf16x8(g);
       }
     }
@@ -216,7 +219,7 @@ stem_tc_kernel(const void* __restrict__ xin, int n, int H, int W, const float* _
   }
 }
 
-template <bool kU8, int OC, int PAD>
+template <bool kU8, int OC, int PAD, int ACT>
 static cudaError_t stem_tc_launch(const void* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
                                   float sc0, float sc1, float sc2, float sh0, float sh1, float sh2, cudaStream_t s) {
   constexpr int NB = (OC + 15) / 16 * 16;
@@ -227,24 +230,39 @@ static cudaError_t stem_tc_launch(const void* x, int n, int h, int w, const floa
   const size_t smem = 1024 + kStT * 128 + NB * 128 + NB * sizeof(float) + 32;
   const int grid = (int)(tiles < (long long)kNumSMs * kStCtasPerSm ? tiles : (long long)kNumSMs * kStCtasPerSm);
   count_launch();
-  return launch_pdl(stem_tc_kernel<kU8, OC, PAD>, dim3(grid), dim3(kStT), smem, s, x, n, h, w, wgt, bias,
+  return launch_pdl(stem_tc_kernel<kU8, OC, PAD, ACT>, dim3(grid), dim3(kStT), smem, s, x, n, h, w, wgt, bias,
                     reinterpret_cast<bf16*>(out), sc0, sc1, sc2, sh0, sh1, sh2);
 }
 
+bool stem_tc_supported(int oc, int pad, int act) {
+  return (oc == 32 && pad == 1 && act == kActSiLU) || (oc == 40 && pad == 0 && act == kActSiLU) ||
+         (oc == 16 && pad == 1 && act == kActGELU) || (oc == 64 && pad == 1 && act == kActReLU);
+}
+
 cudaError_t launch_stem_tc(const float* x, int n, int h, int w, const float* wgt, const float* bias, void* out,
-                           cudaStream_t s, int oc, int pad) {
-  if (oc == 32 && pad == 1) return stem_tc_launch<false, 32, 1>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
-  if (oc == 40 && pad == 0) return stem_tc_launch<false, 40, 0>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
+                           cudaStream_t s, int oc, int pad, int act) {
+  if (oc == 32 && pad == 1 && act == kActSiLU)
+    return stem_tc_launch<false, 32, 1, kActSiLU>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
+  if (oc == 40 && pad == 0 && act == kActSiLU)
+    return stem_tc_launch<false, 40, 0, kActSiLU>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
+  if (oc == 16 && pad == 1 && act == kActGELU)
+    return stem_tc_launch<false, 16, 1, kActGELU>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
+  if (oc == 64 && pad == 1 && act == kActReLU)
+    return stem_tc_launch<false, 64, 1, kActReLU>(x, n, h, w, wgt, bias, out, 0, 0, 0, 0, 0, 0, s);
   return cudaErrorInvalidValue;
 }
 
 cudaError_t launch_stem_tc_u8(const uint8_t* x, int n, int h, int w, const float* wgt, const float* bias, float sc0,
                               float sc1, float sc2, float sh0, float sh1, float sh2, void* out, cudaStream_t s, int oc,
-                              int pad) {
-  if (oc == 32 && pad == 1)
-    return stem_tc_launch<true, 32, 1>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
-  if (oc == 40 && pad == 0)
-    return stem_tc_launch<true, 40, 0>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
+                              int pad, int act) {
+  if (oc == 32 && pad == 1 && act == kActSiLU)
+    return stem_tc_launch<true, 32, 1, kActSiLU>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
+  if (oc == 40 && pad == 0 && act == kActSiLU)
+    return stem_tc_launch<true, 40, 0, kActSiLU>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
+  if (oc == 16 && pad == 1 && act == kActGELU)
+    return stem_tc_launch<true, 16, 1, kActGELU>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
+  if (oc == 64 && pad == 1 && act == kActReLU)
+    return stem_tc_launch<true, 64, 1, kActReLU>(x, n, h, w, wgt, bias, out, sc0, sc1, sc2, sh0, sh1, sh2, s);
   return cudaErrorInvalidValue;
 }
 

@@ -144,27 +144,32 @@ class Engine:
                                                    _ptr(cam), C.c_void_p(base), size, _stream_ptr(dev)))
         return logits, low, cam
 
-    def trunk(self, images: torch.Tensor) -> torch.Tensor:
+    def trunk(self, images: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+        """-> (A [n,C,s,s] fp32 NCHW: the raw output of the reference's Grad-CAM target conv, aux [n,num_classes])."""
         require_cuda_f32(images, "images")
         n = images.shape[0]
         images = images.contiguous()
         a = torch.empty((n, self.feature_channels, self.feature_side, self.feature_side), dtype=torch.float32,
                         device=images.device)
+        aux = torch.zeros((n, self.num_classes), dtype=torch.float32, device=images.device)
         if n == 0:
-            return a
+            return a, aux
         with self._lock, torch.cuda.device(images.device):
             base, size = self._workspace(n)
-            _lib.check(self._lib.b200df_trunk(self._h, _ptr(images), n, _ptr(a), C.c_void_p(base), size,
-                                             _stream_ptr(images.device)))
-        return a
+            _lib.check(self._lib.b200df_trunk_ex(self._h, _ptr(images), n, _ptr(a), _ptr(aux), C.c_void_p(base), size,
+                                                _stream_ptr(images.device)))
+        return a, aux
 
-    def head(self, a: torch.Tensor) -> torch.Tensor:
+    def head(self, a: torch.Tensor, aux: torch.Tensor | None = None) -> torch.Tensor:
         require_cuda_f32(a, "activation")
         a = a.contiguous()
         n = a.shape[0]
         logits = torch.empty((n, self.num_classes), dtype=torch.float32, device=a.device)
+        if aux is None:
+            aux = torch.zeros((n, self.num_classes), dtype=torch.float32, device=a.device)
+        aux = aux.to(dtype=torch.float32).contiguous()
         with self._lock, torch.cuda.device(a.device):
-            _lib.check(self._lib.b200df_head(self._h, _ptr(a), n, _ptr(logits), _stream_ptr(a.device)))
+            _lib.check(self._lib.b200df_head_ex(self._h, _ptr(a), _ptr(aux), n, _ptr(logits), _stream_ptr(a.device)))
         return logits
 
     def head_backward(self, a: torch.Tensor, grad_logits: torch.Tensor) -> torch.Tensor:

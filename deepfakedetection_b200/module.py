@@ -109,12 +109,14 @@ class CamHookPoint(nn.Conv2d):
         return a
 
 
-class B200EfficientNetB0(nn.Module):
-    """Drop-in for ``timm.create_model("efficientnet_b0", num_classes=...)`` in eval mode on a B200."""
+class B200Module(nn.Module):
+    """Lifecycle shared by every backbone served by the engine: timm/efficientnet_pytorch/fastervit-named parameter
+    containers + lazy (re)packing through the C ABI + the hot ``forward`` (orchestrator.py:350-377, 587-592)."""
 
-    arch_id = _lib.ARCH_EFFICIENTNET_B0
-    arch_name = "efficientnet_b0"
+    arch_id = -1
+    arch_name = ""
     default_image_size = 224
+    supports_cam = True
 
     def __init__(self, num_classes: int = 2, precision: str = "bf16") -> None:
         super().__init__()
@@ -127,49 +129,20 @@ class B200EfficientNetB0(nn.Module):
         self._engine = None
         self._engine_id = 0
         self._dirty = True
-        self.register_load_state_dict_post_hook(B200EfficientNetB0._post_load)
+        self.register_load_state_dict_post_hook(B200Module._post_load)
 
     def _build_containers(self, num_classes: int) -> None:
-        self.conv_stem = _Conv(3, 32, 3, 2, 1, bias=False)
-        self.bn1 = _BN(32)
-        stages = []
-        cin = 32
-        for ds, k, s, e, cout, reps in _B0_STAGES:
-            blocks = []
-            for r in range(reps):
-                stride = s if r == 0 else 1
-                blocks.append(_DSBlock(cin, cout, k, stride) if ds else _IRBlock(cin, cout, k, stride, e))
-                cin = cout
-            stages.append(_Seq(*blocks))
-        self.blocks = _Seq(*stages)
-        self.conv_head = CamHookPoint(cin, 1280, 1, bias=False)
-        self.bn2 = _BN(1280)
-        self.classifier = nn.Linear(1280, num_classes)
+        raise NotImplementedError
 
     def _cam_point(self) -> nn.Module:
-        return self.conv_head
+        raise NotImplementedError
 
-    # timm's EfficientNet initialisation, restated: conv N(0, sqrt(2/fan_out)); BN 1/0; linear U(+-1/sqrt(out)).
     def _init_weights(self) -> None:
-        for m in self.modules():
-            if isinstance(m, nn.Conv2d):
-                fan_out = m.kernel_size[0] * m.kernel_size[1] * m.out_channels // m.groups
-                nn.init.normal_(m.weight, 0.0, math.sqrt(2.0 / fan_out))
-                if m.bias is not None:
-                    nn.init.zeros_(m.bias)
-            elif isinstance(m, nn.Linear):
-                bound = 1.0 / math.sqrt(m.weight.size(0))
-                nn.init.uniform_(m.weight, -bound, bound)
-                nn.init.zeros_(m.bias)
-
-    # ---- Grad-CAM target (web_ui.py:108-110 looks for `_conv_head` first) --------------------------
-    @property
-    def _conv_head(self) -> nn.Module:
-        return self.conv_head
+        pass
 
     # ---- weight lifecycle ----------------------------------------------------------------------------
     @staticmethod
-    def _post_load(module: "B200EfficientNetB0", incompatible) -> None:
+    def _post_load(module: "B200Module", incompatible) -> None:
         module._dirty = True
         # the reference loads with strict=False, which hides mistakes; say what did not line up
         if incompatible.missing_keys:
@@ -234,14 +207,29 @@ class B200EfficientNetB0(nn.Module):
             # Grad-CAM hook protocol (web_ui.py:275-279): pytorch-grad-cam hooks `_conv_head` and calls
             # `.register_hook` on its output, so A must be a graph leaf that requires grad.  The trunk has no
             # backward (inference engine): gradients stop at A, which is all Grad-CAM needs.
-            a = ops.trunk(images.detach(), self._engine_id).requires_grad_(True)
-            a = self._cam_point()(a)
-            return ops.head(a, self._engine_id)
+            if not self.supports_cam:
+                raise NotImplementedError(
+                    f"b200 {self.arch_name}: the reference's Grad-CAM target rule (web_ui.py:96-105) picks a conv in front of "
+                    "this network's transformer blocks, so Grad-CAM needs a backward pass through them, which this "
+                    "inference engine does not have.  Call the model under torch.inference_mode()/no_grad().")
+            a, aux = ops.trunk(images.detach(), self._engine_id)
+            a = self._cam_point()(a.requires_grad_(True))
+            return ops.head(a, aux, self._engine_id)
         return ops.forward(images, self._engine_id)
 
     def forward_u8(self, images_hwc: torch.Tensor, mean=(0.485, 0.456, 0.406), std=(0.229, 0.224, 0.225)) -> torch.Tensor:
         """uint8 [N,224,224,3] crops -> logits, with ToTensor + Normalize fused into the stem
         (orchestrator.py:340-345).  Pass ``mean=std=None`` for ``val_normalize: false``."""
+        if images_hwc.ndim != 4 or tuple(images_hwc.shape[1:]) != (224, 224, 3) or images_hwc.dtype != torch.uint8:
+            raise ValueError(f"b200 {self.arch_name} forward_u8 expects uint8 [N,224,224,3] (HWC) crops, got "
+                             f"{images_hwc.dtype} {tuple(images_hwc.shape)}")
+        for name, v in (("mean", mean), ("std", std)):
+            if v is not None and len(v) != 3:
+                raise ValueError(f"{name} must have 3 entries, got {len(v)}")
+        if (mean is None) != (std is None):
+            raise ValueError("pass mean and std together (or both None for `val_normalize: false`)")
+        if not images_hwc.is_cuda:
+            raise RuntimeError(f"images are on '{images_hwc.device}': the b200 backend has no CPU fallback")
         eng = self._ready(images_hwc.device)
         return eng.forward_u8(images_hwc, mean, std)
 
@@ -255,6 +243,51 @@ class B200EfficientNetB0(nn.Module):
         if targets is not None:
             targets = targets.to(device=images.device, dtype=torch.int32)
         return ops.forward_cam(images.float(), targets, self._engine_id)
+
+
+class B200EfficientNetB0(B200Module):
+    """Drop-in for ``timm.create_model("efficientnet_b0", num_classes=...)`` in eval mode on a B200."""
+
+    arch_id = _lib.ARCH_EFFICIENTNET_B0
+    arch_name = "efficientnet_b0"
+
+    def _build_containers(self, num_classes: int) -> None:
+        self.conv_stem = _Conv(3, 32, 3, 2, 1, bias=False)
+        self.bn1 = _BN(32)
+        stages = []
+        cin = 32
+        for ds, k, s, e, cout, reps in _B0_STAGES:
+            blocks = []
+            for r in range(reps):
+                stride = s if r == 0 else 1
+                blocks.append(_DSBlock(cin, cout, k, stride) if ds else _IRBlock(cin, cout, k, stride, e))
+                cin = cout
+            stages.append(_Seq(*blocks))
+        self.blocks = _Seq(*stages)
+        self.conv_head = CamHookPoint(cin, 1280, 1, bias=False)
+        self.bn2 = _BN(1280)
+        self.classifier = nn.Linear(1280, num_classes)
+
+    def _cam_point(self) -> nn.Module:
+        return self.conv_head
+
+    # timm's EfficientNet initialisation, restated: conv N(0, sqrt(2/fan_out)); BN 1/0; linear U(+-1/sqrt(out)).
+    def _init_weights(self) -> None:
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                fan_out = m.kernel_size[0] * m.kernel_size[1] * m.out_channels // m.groups
+                nn.init.normal_(m.weight, 0.0, math.sqrt(2.0 / fan_out))
+                if m.bias is not None:
+                    nn.init.zeros_(m.bias)
+            elif isinstance(m, nn.Linear):
+                bound = 1.0 / math.sqrt(m.weight.size(0))
+                nn.init.uniform_(m.weight, -bound, bound)
+                nn.init.zeros_(m.bias)
+
+    # ---- Grad-CAM target (web_ui.py:108-110 looks for `_conv_head` first) --------------------------
+    @property
+    def _conv_head(self) -> nn.Module:
+        return self.conv_head
 
 
 # ---- the reference's registry default: efficientnet_pytorch EfficientNet-B3 ---------------------------------------

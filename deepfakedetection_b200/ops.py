@@ -45,23 +45,25 @@ def _(images, engine):
 
 
 @torch.library.custom_op("b200df::trunk", mutates_args=(), device_types="cuda")
-def trunk(images: torch.Tensor, engine: int) -> torch.Tensor:
-    return _engine(engine).trunk(images)
+def trunk(images: torch.Tensor, engine: int) -> tuple[torch.Tensor, torch.Tensor]:
+    a, aux = _engine(engine).trunk(images)
+    return a, aux
 
 
 @trunk.register_fake
 def _(images, engine):
     e = _engine(engine)
-    return images.new_empty((images.shape[0], e.feature_channels, e.feature_side, e.feature_side), dtype=torch.float32)
+    return (images.new_empty((images.shape[0], e.feature_channels, e.feature_side, e.feature_side), dtype=torch.float32),
+            images.new_empty((images.shape[0], e.num_classes), dtype=torch.float32))
 
 
 @torch.library.custom_op("b200df::head", mutates_args=(), device_types="cuda")
-def head(a: torch.Tensor, engine: int) -> torch.Tensor:
-    return _engine(engine).head(a)
+def head(a: torch.Tensor, aux: torch.Tensor, engine: int) -> torch.Tensor:
+    return _engine(engine).head(a, aux)
 
 
 @head.register_fake
-def _(a, engine):
+def _(a, aux, engine):
     return a.new_empty((a.shape[0], _engine(engine).num_classes), dtype=torch.float32)
 
 
@@ -76,14 +78,14 @@ def _(a, grad_logits, engine):
 
 
 def _head_setup(ctx, inputs, output):
-    a, engine = inputs
+    a, _aux, engine = inputs
     ctx.save_for_backward(a)
     ctx.engine = engine
 
 
 def _head_bwd(ctx, grad_logits):
     (a,) = ctx.saved_tensors
-    return head_backward(a, grad_logits.contiguous(), ctx.engine), None
+    return head_backward(a, grad_logits.contiguous(), ctx.engine), None, None
 
 
 head.register_autograd(_head_bwd, setup_context=_head_setup)

@@ -14,6 +14,9 @@ B200 engine module, so ``load_model`` (/root/reference/orchestration/orchestrato
 * ``efficientnet_b0.b200_fp32``  -- strict fp32 path (|dlogit| <= 1e-3 vs the timm fp32 forward)
 * ``efficientnet_b3`` / ``efficientnet_b3.b200_fp32`` -- the registry's own default entry (efficientnet_pytorch
   layout, model_registry.py:32-36, 50-58), so ``config/inference.yaml`` and the release weights run as they are
+* ``efficientformerv2_s1`` (timm layout, model_registry.py:39-40) and ``faster_vit_0_224`` / ``faster_vit_2_224``
+  (fastervit layout, model_registry.py:43-47): exact entries that win over the registry's prefix table (:60-75, 87-88),
+  so the other two models of ``config/inference.yaml`` run on the engine too; each also as ``<name>.b200_fp32``
 """
 
 from __future__ import annotations
@@ -56,6 +59,34 @@ def build_efficientnet_b3(model_name: str, num_classes: int) -> nn.Module:
     return B200EfficientNetB3(num_classes=num_classes, precision=_precision_for(model_name))
 
 
+def build_efficientformerv2_s1(model_name: str, num_classes: int) -> nn.Module:
+    """Replaces ``_build_efficientformer`` (model_registry.py:39-40) for timm ``efficientformerv2_s1``."""
+    from .module_vit import B200EfficientFormerV2S1
+
+    return B200EfficientFormerV2S1(num_classes=num_classes, precision=_precision_for(model_name))
+
+
+def build_fastervit(model_name: str, num_classes: int) -> nn.Module:
+    """Replaces ``_build_fastervit`` (model_registry.py:43-47): ``faster_vit_0_224`` / ``faster_vit_2_224`` + fresh head."""
+    from .module_vit import B200FasterViT
+
+    variant = model_name[: -len(".b200_fp32")] if model_name.endswith(".b200_fp32") else model_name
+    return B200FasterViT(num_classes=num_classes, precision=_precision_for(model_name), variant=variant)
+
+
+def _vit_entries() -> dict[str, dict[str, Any]]:
+    out: dict[str, dict[str, Any]] = {}
+    # same train_module / weights_key / image size the reference's prefix table yields (model_registry.py:60-75, 90-96)
+    for name, train, builder in (
+        ("efficientformerv2_s1", "trainers.efficientformer_v2", build_efficientformerv2_s1),
+        ("faster_vit_0_224", "trainers.fastervit", build_fastervit),
+        ("faster_vit_2_224", "trainers.fastervit", build_fastervit),
+    ):
+        for suffix in ("", ".b200_fp32"):
+            out[name + suffix] = {"train_module": train, "weights_key": name, "default_image_size": 224, "builder": builder}
+    return out
+
+
 SERVED: dict[str, dict[str, Any]] = {
     # the reference's own exact entry (model_registry.py:50-58), same train_module / weights_key / image size
     "efficientnet_b3": {
@@ -83,6 +114,8 @@ SERVED: dict[str, dict[str, Any]] = {
         "builder": build_efficientnet_b0,
     },
 }
+
+SERVED.update(_vit_entries())
 
 # our own table, same lookup semantics as the reference's get_model_spec
 _LOCAL_SPECS: dict[str, ModelSpec] = {

@@ -54,6 +54,11 @@ extern "C" {
 #define B200DF_ARCH_EFFICIENTNET_B0 0 /* timm `efficientnet_b0` state_dict layout (conv_stem, blocks.S.R.*, ...)     */
 #define B200DF_ARCH_EFFICIENTNET_B3 1 /* efficientnet_pytorch `efficientnet-b3` layout (_conv_stem, _blocks.N.*, _fc): */
                                       /* the reference's registry default, orchestration/model_registry.py:32-36,50-58 */
+#define B200DF_ARCH_EFFICIENTFORMERV2_S1 2 /* timm `efficientformerv2_s1` layout (stem.conv1.conv, stages.S.blocks.B.*,  */
+                                           /* norm, head, head_dist): model_registry.py:39-40, 61-67                     */
+#define B200DF_ARCH_FASTERVIT_0 3 /* fastervit `faster_vit_0_224` layout (patch_embed.conv_down.N, levels.L.blocks.B.*,  */
+                                  /* norm, head): model_registry.py:43-47, 68-74                                         */
+#define B200DF_ARCH_FASTERVIT_2 4 /* fastervit `faster_vit_2_224`, the registry's prefix-table default (:68-74)           */
 
 /* precisions (b200df_finalize) */
 #define B200DF_PREC_BF16 0 /* bf16 NHWC activations/weights, fp32 accumulate, tcgen05 GEMMs */
@@ -120,6 +125,13 @@ int b200df_trunk(b200df_handle h, const float* images, int n, float* a_nchw, voi
 int b200df_head(b200df_handle h, const float* a_nchw, int n, float* logits, void* stream);
 int b200df_head_backward(b200df_handle h, const float* a_nchw, const float* grad_logits, int n,
                          float* grad_a_nchw, void* stream);
+/* Same split with an auxiliary per-image term, aux float32 [n,num_classes]: EfficientFormerV2's Grad-CAM target
+ * (the last nn.Conv2d, `stages.3.blocks.5.mlp.fc2.conv`, web_ui.py:96-105) is followed by an AFFINE map whose offset
+ * depends on the block's residual input, not on A: trunk_ex writes aux = logits - lin(A), head_ex(A, aux) = aux + lin(A).
+ * The EfficientNet engines write / ignore zeros.  FasterViT has no split path (B200DF_E_STATE). */
+int b200df_trunk_ex(b200df_handle h, const float* images, int n, float* a_nchw, float* aux, void* workspace,
+                    size_t workspace_bytes, void* stream);
+int b200df_head_ex(b200df_handle h, const float* a_nchw, const float* aux, int n, float* logits, void* stream);
 
 /* softmax + argmax of [n,num_classes] logits packed as records {p[0..C), pred, label} of
  * (C+2) floats per image -- the buffer the multi-GPU harness all-gathers. labels may be NULL. */
@@ -166,6 +178,15 @@ int b200df_profile_count(b200df_handle h);
 int b200df_profile_get(b200df_handle h, int index, const char** name, float* ms, double* bytes,
                        double* flops);
 int b200df_profile_reset(b200df_handle h);
+
+/* ---- debug checkpoints (layer programs: EfficientFormerV2 / FasterViT) --------------------- */
+/* A mark says: after op `op` of the forward, the workspace at `ws_offset` (for batch n) holds sequences of
+ * seqs_rows_c[0] rows x seqs_rows_c[3] channels (engine dtype), of which rows [seqs_rows_c[1], +seqs_rows_c[2]) equal the
+ * reference module output `name` (token-major / NHWC).  b200df_debug_stop_after(h, op) makes forward return after that
+ * op (-1 = run everything) so the buffer can be read before later layers reuse it.  Test / tooling use only. */
+int b200df_debug_num_marks(b200df_handle h);
+int b200df_debug_mark(b200df_handle h, int index, int n, const char** name, int* op, int* seqs_rows_c, size_t* ws_offset);
+int b200df_debug_stop_after(b200df_handle h, int op);
 
 /* ---- per-kernel entry points (unit tests, ncu) ------------------------------------------ */
 /* dtype: 0 = bf16, 1 = fp32 for activations/weights; all layouts NHWC; bias fp32. */
