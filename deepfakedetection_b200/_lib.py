@@ -73,6 +73,13 @@ SIGNATURES: dict[str, tuple] = {
     "b200df_k_head_pool": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "b200df_k_cam": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp]),
     "b200df_k_cam_upsample": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "b200df_k_stem_act": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "b200df_k_dwconv_act": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp]),
+    "b200df_k_conv3x3": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _vp]),
+    "b200df_k_attention": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp,
+                                _vp, _i, _vp, _i, _vp]),
+    "b200df_k_layernorm": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _f, _i, _vp]),
+    "b200df_k_upsample2x_act": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
 }
 
 _lib = None

@@ -18,7 +18,7 @@ template <typename T>
 __global__ void __launch_bounds__(CThreads)
 conv3x3_simt_kernel(const T* __restrict__ x, int n, int H, int W, int Cin, int Cout, int stride,
                     const T* __restrict__ w, const float* __restrict__ bias, const T* __restrict__ residual, int act,
-                    T* __restrict__ out, int Ho, int Wo) {
+                    T* __restrict__ out, int Ho, int Wo, int cinp) {
   __shared__ float As[CBK][CBM + 1];
   __shared__ float Bs[CBK][CBN + 1];
   __shared__ int s_img[CBM], s_iy[CBM], s_ix[CBM];
@@ -43,6 +43,7 @@ conv3x3_simt_kernel(const T* __restrict__ x, int n, int H, int W, int Cin, int C
   }
   __syncthreads();
   const int K = 9 * Cin;
+  const size_t wrow = (size_t)9 * cinp;   // weight row pitch: every tap holds cinp (>= Cin) channels
   float acc[4][4];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -65,7 +66,10 @@ conv3x3_simt_kernel(const T* __restrict__ x, int n, int H, int W, int Cin, int C
       for (int j = 0; j < 8; ++j) As[ch * 8 + j][r] = v[j];
     } else {  // B: thread = (output channel, 8-element chunk of its K row)
       const int t = tid - 2 * CBM, cidx = t >> 1, ch = t & 1, k8 = k0 + ch * 8, co = n0 + cidx;
-      if (k8 < K && co < Cout) load8<T>(w + (size_t)co * K + k8, v);
+      if (k8 < K && co < Cout) {
+        const int tap = k8 / Cin, c = k8 - tap * Cin;
+        load8<T>(w + (size_t)co * wrow + (size_t)tap * cinp + c, v);
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) Bs[ch * 8 + j][cidx] = v[j];
     }
@@ -101,20 +105,21 @@ conv3x3_simt_kernel(const T* __restrict__ x, int n, int H, int W, int Cin, int C
 
 cudaError_t launch_conv3x3_simt(const void* x, int n, int h, int w, int cin, int cout, int stride, const void* wgt,
                                 const float* bias, const void* residual, int act, void* out, int dtype,
-                                cudaStream_t s) {
+                                cudaStream_t s, int cinp) {
   if (n <= 0) return cudaSuccess;
-  if (cin % 8 || (stride != 1 && stride != 2)) return cudaErrorInvalidValue;
+  if (cinp <= 0) cinp = cin;
+  if (cin % 8 || cinp % 8 || cinp < cin || (stride != 1 && stride != 2)) return cudaErrorInvalidValue;
   const int Ho = (h - 1) / stride + 1, Wo = (w - 1) / stride + 1;  // pad 1, k 3
   const long long M = (long long)n * Ho * Wo;
   dim3 grid((unsigned)((M + CBM - 1) / CBM), (cout + CBN - 1) / CBN);
   if (dtype == kBF16) {
     conv3x3_simt_kernel<bf16><<<grid, CThreads, 0, s>>>(
         reinterpret_cast<const bf16*>(x), n, h, w, cin, cout, stride, reinterpret_cast<const bf16*>(wgt), bias,
-        reinterpret_cast<const bf16*>(residual), act, reinterpret_cast<bf16*>(out), Ho, Wo);
+        reinterpret_cast<const bf16*>(residual), act, reinterpret_cast<bf16*>(out), Ho, Wo, cinp);
   } else {
     conv3x3_simt_kernel<float><<<grid, CThreads, 0, s>>>(
         reinterpret_cast<const float*>(x), n, h, w, cin, cout, stride, reinterpret_cast<const float*>(wgt), bias,
-        reinterpret_cast<const float*>(residual), act, reinterpret_cast<float*>(out), Ho, Wo);
+        reinterpret_cast<const float*>(residual), act, reinterpret_cast<float*>(out), Ho, Wo, cinp);
   }
   count_launch();
   return cudaGetLastError();

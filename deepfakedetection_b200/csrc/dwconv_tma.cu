@@ -313,7 +313,8 @@ typedef CUresult (*PFN_encodeTiledNd)(CUtensorMap*, CUtensorMapDataType, cuuint3
                                       CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsigned long long* dims,
-                        const unsigned long long* strides_bytes, const unsigned* box, int swizzle) {
+                        const unsigned long long* strides_bytes, const unsigned* box, int swizzle,
+                        const unsigned* elem_strides) {
   static PFN_encodeTiledNd enc = nullptr;
   if (!enc) {
     void* fn = nullptr;
@@ -329,7 +330,7 @@ int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsign
   for (int i = 0; i < rank; ++i) {
     gdim[i] = dims[i];
     bx[i] = box[i];
-    es[i] = 1;
+    es[i] = elem_strides ? elem_strides[i] : 1;
     if (i > 0) {
       gstr[i - 1] = strides_bytes[i];
       if (strides_bytes[i] % 16) return -2;

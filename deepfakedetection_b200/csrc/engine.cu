@@ -624,11 +624,27 @@ int run_gemm(b200df_engine* h, Plan& plan, const GemmCall& g, int index, cudaStr
 
 enum InputKind { kInF32NCHW = 0, kInU8HWC = 1 };
 
-// dense 3x3 conv of a layer program: tcgen05 implicit GEMM when the shape allows it (bf16), CUDA-core GEMM otherwise
+// dense 3x3 conv of a layer program: tcgen05 implicit GEMM on the bf16 path, CUDA-core implicit GEMM otherwise
+// (B200DF_GEMM=simt, or B200DF_CONV_TC_S2=0 for the stride-2 layers only: debugging aids)
 int run_conv3(b200df_engine* h, Plan& plan, int index, const void* x, int n, int hin, int cin, int cout, int stride,
-              const void* w, const float* bias, const void* residual, int act, void* out, int dt, cudaStream_t s) {
-  (void)plan; (void)index;
-  CU_OK(launch_conv3x3_simt(x, n, hin, hin, cin, cout, stride, w, bias, residual, act, out, dt, s));
+              const void* w, const float* bias, const void* residual, int act, void* out, int dt, cudaStream_t s,
+              int cinp, int cout_pad, int bn) {
+  static int tc_s2 = -1;
+  if (tc_s2 < 0) {
+    const char* e = getenv("B200DF_CONV_TC_S2");
+    tc_s2 = (e && e[0] == '0') ? 0 : 1;
+  }
+  if (dt == kBF16 && h->gemm_impl == 0 && (stride == 1 || tc_s2)) {
+    Conv3Plan& cp = plan.convs[index];
+    if (cp.x != x || cp.out != out || cp.n != n) {
+      cp.x = nullptr;
+      if (plan_conv3x3_tc(cp, x, n, hin, hin, cin, cout, cout_pad, bn, stride, w, bias, residual, act, out) != 0)
+        return fail(B200DF_E_CUDA, "tcgen05 3x3 conv: cannot plan op %d (cin %d cout %d stride %d)", index, cin, cout, stride);
+    }
+    CU_OK(launch_conv3x3_tc(cp, s));
+    return B200DF_OK;
+  }
+  CU_OK(launch_conv3x3_simt(x, n, hin, hin, cin, cout, stride, w, bias, residual, act, out, dt, s, cinp));
   return B200DF_OK;
 }
 
@@ -1184,3 +1200,83 @@ extern "C" int b200df_k_cam_upsample(const float* cam_lowres, int n, int side, i
   CU_OK(launch_cam_upsample(cam_lowres, n, side, out_side, cam, S(stream)));
   return B200DF_OK;
 }
+
+// ---- per-kernel entry points of the transformer-style backbones ------------------------------------------------------
+extern "C" int b200df_k_stem_act(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias, void* out,
+                                 int dtype, int oc, int pad, int act, void* stream) {
+  CU_OK(launch_stem(x_nchw, n, h, w, wgt, bias, out, dtype, S(stream), oc, pad, act));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_dwconv_act(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
+                                   const float* bias, void* out, int act, int dtype, void* stream) {
+  CU_OK(launch_dwconv(x, n, h, w, c, k, stride, wgt, bias, out, nullptr, dtype, S(stream), -1, act));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_conv3x3(const void* x, int n, int h, int w, int cin, int cout, int stride, const void* wgt,
+                                const float* bias, const void* residual, int act, void* out, int dtype, int impl,
+                                void* stream) {
+  if (impl == 1 || dtype != kBF16) {
+    CU_OK(launch_conv3x3_simt(x, n, h, w, cin, cout, stride, wgt, bias, residual, act, out, dtype, S(stream)));
+    return B200DF_OK;
+  }
+  if (cin % 8 || cout % 8) return fail(B200DF_E_INVALID, "cin and cout must be multiples of 8");
+  // test-only convenience: re-lay the [cout, 9*cin] weights out as [cout_pad, 9, cin_pad] on the fly (the engine does
+  // this once in finalize)
+  int cout_pad = 0;
+  const int bn = choose_bn(cout, &cout_pad), cinp = conv3x3_tc_cin_pad(cin);
+  cudaStream_t s = S(stream);
+  void* wpad = nullptr;
+  float* bpad = nullptr;
+  CU_OK(cudaMalloc(&wpad, (size_t)cout_pad * 9 * cinp * 2));
+  CU_OK(cudaMalloc(&bpad, (size_t)cout_pad * sizeof(float)));
+  CU_OK(cudaMemsetAsync(wpad, 0, (size_t)cout_pad * 9 * cinp * 2, s));
+  CU_OK(cudaMemsetAsync(bpad, 0, (size_t)cout_pad * sizeof(float), s));
+  CU_OK(cudaMemcpy2DAsync(wpad, (size_t)cinp * 2, wgt, (size_t)cin * 2, (size_t)cin * 2, (size_t)cout * 9,
+                          cudaMemcpyDeviceToDevice, s));
+  CU_OK(cudaMemcpyAsync(bpad, bias, (size_t)cout * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  Conv3Plan plan;
+  int rc = B200DF_OK;
+  if (plan_conv3x3_tc(plan, x, n, h, w, cin, cout, cout_pad, bn, stride, wpad, bpad, residual, act, out) != 0) {
+    rc = fail(B200DF_E_INVALID, "shape not supported by the tcgen05 3x3 conv (cin %d cout %d stride %d act %d)", cin, cout,
+              stride, act);
+  } else {
+    cudaError_t e = launch_conv3x3_tc(plan, s);
+    if (e != cudaSuccess) rc = fail(B200DF_E_CUDA, "launch_conv3x3_tc: %s", cudaGetErrorString(e));
+  }
+  cudaError_t es = cudaStreamSynchronize(s);
+  cudaFree(wpad);
+  cudaFree(bpad);
+  if (rc == B200DF_OK && es != cudaSuccess) rc = fail(B200DF_E_CUDA, "conv3x3_tc execution: %s", cudaGetErrorString(es));
+  return rc;
+}
+
+extern "C" int b200df_k_attention(const void* q, const void* k, const void* v, int q_pitch, int k_pitch, int v_pitch,
+                                  int q_off, int k_off, int v_off, int nseq, int nq, int nk, int dk, int dv, int heads,
+                                  float scale, const float* bias, const float* th1_w, const float* th1_b,
+                                  const float* th2_w, const float* th2_b, const void* vlocal, int act, void* out,
+                                  int dtype, void* stream) {
+  AttnArgs a;
+  memset(&a, 0, sizeof(a));
+  a.q = q; a.k = k; a.v = v;
+  a.q_pitch = q_pitch; a.k_pitch = k_pitch; a.v_pitch = v_pitch;
+  a.q_off = q_off; a.k_off = k_off; a.v_off = v_off;
+  a.nseq = nseq; a.nq = nq; a.nk = nk; a.dk = dk; a.dv = dv; a.heads = heads; a.scale = scale;
+  a.bias = bias; a.th1_w = th1_w; a.th1_b = th1_b; a.th2_w = th2_w; a.th2_b = th2_b;
+  a.vlocal = vlocal; a.act = act; a.out = out;
+  CU_OK(launch_attention(a, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_layernorm(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c,
+                                  float eps, int dtype, void* stream) {
+  CU_OK(launch_layernorm(x, y, gamma, beta, rows, c, eps, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_upsample2x_act(const void* x, void* y, int n, int side, int c, int act, int dtype, void* stream) {
+  CU_OK(launch_upsample2x_act(x, y, n, side, c, act, dtype, S(stream)));
+  return B200DF_OK;
+}
+

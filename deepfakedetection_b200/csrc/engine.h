@@ -56,6 +56,7 @@ struct Plan {  // cached tensor maps for one (n, workspace) pair; the engine kee
   unsigned long long stamp = 0;   // last use
   std::vector<TcGemmArgs> gemms;  // in schedule order
   std::vector<DwPlan> dws;        // per block (bf16 path); x == nullptr -> not planned yet
+  std::vector<Conv3Plan> convs;   // per op of a layer program (tcgen05 3x3 convs)
 };
 
 // Per-launch profiling record (b200df_set_profile): CUDA events around one kernel launch plus

@@ -1,6 +1,7 @@
 // Host-side launcher declarations shared by the engine and the C-ABI per-kernel entry points.
 #pragma once
 
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -111,8 +112,10 @@ int plan_dwconv_tma(DwPlan& plan, const void* x, int n, int h, int w, int c, int
                     const float* bias, void* out, pool_t* pool, int pad_lo = -1, int act = 1);
 cudaError_t launch_dwconv_tma(const DwPlan& plan, cudaStream_t s);
 // Generic N-d bf16 tensor map (dims/strides innermost first; strides[0] is implicit).  0 on success.
+// elem_strides (nullable): traversal stride per dim -- a box of B elements then loads ceil(B / stride) elements.
 int encode_tmap_nd_bf16(void* tmap_out, const void* base, int rank, const unsigned long long* dims,
-                        const unsigned long long* strides_bytes, const unsigned* box, int swizzle);
+                        const unsigned long long* strides_bytes, const unsigned* box, int swizzle,
+                        const unsigned* elem_strides = nullptr);
 
 cudaError_t launch_se(const pool_t* pool, int n, int c, int rd, float inv_hw, const float* w1, const float* b1,
                       const float* w2, const float* b2, float* gate, cudaStream_t s);
@@ -170,9 +173,38 @@ cudaError_t launch_softmax_pack(const float* logits, const int64_t* labels, int 
 
 // ---- dense 3x3 conv (conv3x3.cu: CUDA-core implicit GEMM, any dtype; conv3x3_tc.cu: tcgen05, bf16) ----------------
 // x NHWC [n, h, w, cin]; wgt [cout, 9*cin] with k = (ky*3 + kx)*cin + c in the engine dtype; pad 1; stride 1 | 2.
+// cinp: channel pitch of one tap inside a weight row (>= cin; the tcgen05 layout pads every tap to 64 channels).
 cudaError_t launch_conv3x3_simt(const void* x, int n, int h, int w, int cin, int cout, int stride, const void* wgt,
                                 const float* bias, const void* residual, int act, void* out, int dtype,
-                                cudaStream_t s);
+                                cudaStream_t s, int cinp = 0);
+
+// tcgen05 implicit GEMM (conv3x3_tc.cu), bf16.  wgt_tc: [cout_pad, 9, cin_pad] bf16, cin_pad = conv3x3_tc_cin_pad(cin),
+// rows >= cout and channels >= cin zero; bias [cout_pad]; (cout_pad, bn) as chosen by the engine (choose_bn).
+struct ConvTcParams {
+  int cin, cout, cout_pad, bn;
+  int Ho, Wo, stride, n_img;
+  int th, ti;                     // M tile: 8 wide x th tall x ti images (th * ti = 16)
+  int tiles_x, tiles_y, groups;   // spatial tiles per image, image groups
+  int cpt, k_chunks;              // 64-channel chunks per tap, 9 * cpt
+  int n_tiles, num_tiles, stages, acc_stride;
+  uint32_t tmem_cols;
+  const float* bias;
+  const __nv_bfloat16* residual;
+};
+struct Conv3Plan {
+  alignas(64) unsigned char tmap_x[128];
+  alignas(64) unsigned char tmap_w[128];
+  alignas(64) unsigned char tmap_out[128];
+  ConvTcParams p;
+  int act = 0, grid = 0, n = 0;
+  size_t smem = 0;
+  const void* x = nullptr;   // cache key
+  void* out = nullptr;
+};
+int conv3x3_tc_cin_pad(int cin);
+int plan_conv3x3_tc(Conv3Plan& plan, const void* x, int n, int h, int w, int cin, int cout, int cout_pad, int bn,
+                    int stride, const void* wgt_tc, const float* bias, const void* residual, int act, void* out);
+cudaError_t launch_conv3x3_tc(const Conv3Plan& plan, cudaStream_t s);
 
 // ---- small-sequence attention (attn.cu) ---------------------------------------------------------------------------
 struct AttnArgs {

@@ -53,13 +53,14 @@ class GradCAM:
         return False
 
     def _fused_ok(self) -> bool:
-        from .module import B200EfficientNetB0
+        from .module import B200Module
 
         return (
             not self.use_hooks
-            and isinstance(self.model, B200EfficientNetB0)
+            and isinstance(self.model, B200Module)
+            and self.model.supports_cam
             and len(self.target_layers) == 1
-            and self.target_layers[0] is self.model._conv_head
+            and self.target_layers[0] is self.model._cam_point()
             and self.reshape_transform is None
         )
 

@@ -239,6 +239,37 @@ int b200df_k_cam(const void* a, int n, int hw, int c, const float* scale, const 
 int b200df_k_cam_upsample(const float* cam_lowres, int n, int side, int out_side, float* cam,
                           void* stream);
 
+/* ---- kernels of the transformer-style backbones (EfficientFormerV2 / FasterViT) ---- */
+/* act everywhere: 0 none, 1 SiLU, 2 GELU (nn.GELU, erf form; the bf16 path evaluates the tanh form), 3 ReLU. */
+
+/* Stem with `oc` in {16, 32, 40, 64} output channels and activation `act` (timm efficientformerv2 `stem.conv1`:
+ * oc 16 GELU; fastervit `patch_embed.conv_down.0`: oc 64 ReLU). */
+int b200df_k_stem_act(const float* x_nchw, int n, int h, int w, const float* wgt, const float* bias, void* out,
+                      int dtype, int oc, int pad, int act, void* stream);
+
+/* Depthwise kxk + bias + `act` (no pooling): EfficientFormerV2 `mlp.mid` (GELU), `stride_conv` / `v_local` (none). */
+int b200df_k_dwconv_act(const void* x, int n, int h, int w, int c, int k, int stride, const float* wgt,
+                        const float* bias, void* out, int act, int dtype, void* stream);
+
+/* Dense 3x3 conv, pad 1, stride 1|2: out[n,ho,wo,cout] = act(conv(x) + bias) (+ residual).  x NHWC [n,h,w,cin];
+ * wgt [cout, 9*cin] with k = (ky*3 + kx)*cin + c, in `dtype`.  impl: 0 = tcgen05 implicit GEMM (bf16), 1 = SIMT. */
+int b200df_k_conv3x3(const void* x, int n, int h, int w, int cin, int cout, int stride, const void* wgt,
+                     const float* bias, const void* residual, int act, void* out, int dtype, int impl, void* stream);
+
+/* Small-sequence attention: S = q k^T * scale + bias [heads,nq,nk]; optional talking-head 1x1 mixes across heads
+ * before / after the softmax; out = P v (+ vlocal) then `act`.  Token rows: pitch elements, head h at off + h*d. */
+int b200df_k_attention(const void* q, const void* k, const void* v, int q_pitch, int k_pitch, int v_pitch, int q_off,
+                       int k_off, int v_off, int nseq, int nq, int nk, int dk, int dv, int heads, float scale,
+                       const float* bias, const float* th1_w, const float* th1_b, const float* th2_w,
+                       const float* th2_b, const void* vlocal, int act, void* out, int dtype, void* stream);
+
+/* LayerNorm over the innermost dim of [rows, c]. */
+int b200df_k_layernorm(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c, float eps,
+                       int dtype, void* stream);
+
+/* nn.Upsample(scale_factor=2, mode="bilinear") + act on NHWC [n,side,side,c] -> [n,2 side,2 side,c]. */
+int b200df_k_upsample2x_act(const void* x, void* y, int n, int side, int c, int act, int dtype, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

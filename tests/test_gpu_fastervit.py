@@ -1,0 +1,135 @@
+"""End-to-end parity on a B200 for FasterViT-0 (BASELINE.json configs[4]) and FasterViT-2 (the
+reference registry's default `faster_vit` entry, model_registry.py:68-74): registered backend module vs
+the fp32 oracle on identical synthetic inputs and weights.  fp32 path max |dlogit| <= 1e-3; bf16 path max |dsoftmax|
+<= 2e-2 with >= 99.9 % argmax agreement."""
+
+import pytest
+import torch
+
+from deepfakedetection_b200 import _lib, registry
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _need_gpu():
+    assert torch.cuda.is_available() and _lib.lib().b200df_device_count() > 0, "these tests need a B200"
+    torch.cuda.set_device(0)
+
+
+def build(oracle, name):
+    model = registry.get_model_spec(name).builder(name, 2)
+    model.to(torch.device("cuda")).eval()
+    model.load_state_dict(oracle.state_dict(), strict=False)
+    return model
+
+
+@pytest.fixture(scope="module", params=["faster_vit_0_224", "faster_vit_2_224"])
+def calibrated(request):
+    from oracle.effnet_b0 import synth_images
+    from oracle.fastervit import make_calibrated_oracle
+
+    m = make_calibrated_oracle(seed=0, variant=request.param)
+    x = synth_images(16, seed=11)
+    with torch.no_grad():
+        ref = m(x)
+    return request.param, m, x, ref
+
+
+def test_layer_by_layer_fp32():
+    import sys
+    from pathlib import Path
+
+    sys.path.insert(0, str(Path(__file__).resolve().parent.parent / "tools"))
+    import layer_diff
+
+    assert layer_diff.main("faster_vit_0_224", "fp32", 2) == 0
+
+
+def test_fp32_path_logits(calibrated):
+    name, m, x, ref = calibrated
+    model = build(m, name + ".b200_fp32")
+    with torch.inference_mode():
+        out = model(x.cuda())
+    assert out.shape == ref.shape and out.dtype == torch.float32
+    assert ref.std().item() > 0.5
+    err = (out.cpu() - ref).abs().max().item()
+    assert err <= 1e-3, f"{name}: max |dlogit| = {err}"
+    for n in (1, 5):
+        with torch.inference_mode():
+            o = model(x[:n].cuda()).cpu()
+        assert (o - ref[:n]).abs().max().item() <= 1e-3, n
+
+
+def test_bf16_path_on_calibrated_weights(calibrated):
+    name, m, x, ref = calibrated
+    model = build(m, name)
+    with torch.inference_mode():
+        out = model(x.cuda()).cpu()
+    rel = ((out - ref).pow(2).mean().sqrt() / ref.std()).item()
+    assert rel <= 0.06, f"{name}: rms logit error / logit std = {rel}"
+
+
+def test_bf16_path_softmax_and_argmax_2048():
+    """north_star tolerance on 8 batches of 256 images for FasterViT-0."""
+    from oracle.effnet_b0 import synth_images
+    from oracle.fastervit import make_seeded_oracle
+
+    ref_model = make_seeded_oracle(seed=0)
+    model = build(ref_model, "faster_vit_0_224")
+    worst, agree, total, refs, outs = 0.0, 0, 0, [], []
+    for b in range(8):
+        x = synth_images(256, seed=200 + b)
+        with torch.no_grad():
+            ref = ref_model(x)
+        with torch.inference_mode():
+            out = model(x.cuda()).cpu()
+        worst = max(worst, (torch.softmax(out, 1) - torch.softmax(ref, 1)).abs().max().item())
+        agree += (out.argmax(1) == ref.argmax(1)).sum().item()
+        total += x.shape[0]
+        refs.append(ref)
+        outs.append(out)
+    ref, out = torch.cat(refs), torch.cat(outs)
+    assert worst <= 2e-2, f"max |dsoftmax| = {worst}"
+    assert agree / total >= 0.999, f"argmax agreement {agree}/{total}"
+    rel = ((out - ref).pow(2).mean().sqrt() / ref.std()).item()
+    assert rel <= 0.05, f"rms logit error / logit std = {rel}"
+
+
+def test_bf16_simt_paths_agree_with_tcgen05(monkeypatch):
+    from oracle.effnet_b0 import synth_images
+    from oracle.fastervit import make_seeded_oracle
+
+    ref_model = make_seeded_oracle(seed=0)
+    x = synth_images(8, seed=3).cuda()
+    monkeypatch.setenv("B200DF_GEMM", "simt")
+    simt = build(ref_model, "faster_vit_0_224")
+    with torch.inference_mode():
+        a = simt(x).cpu()
+    monkeypatch.delenv("B200DF_GEMM")
+    tc = build(ref_model, "faster_vit_0_224")
+    with torch.inference_mode():
+        b = tc(x).cpu()
+    with torch.no_grad():
+        ref = ref_model(x.cpu())
+    assert (a - b).pow(2).mean().sqrt().item() <= 0.05 * ref.std().item()
+
+
+def test_gradcam_is_refused_loudly():
+    """The reference's target rule picks `levels.2.global_tokenizer.pos_embed` (web_ui.py:96-105): a backward pass through
+    11 transformer blocks, which the inference engine does not have -- it must say so, not return a wrong map."""
+    from oracle.fastervit import make_seeded_oracle
+
+    ref_model = make_seeded_oracle(seed=0)
+    model = build(ref_model, "faster_vit_0_224")
+    last = None
+    for name, mod in model.named_modules():
+        if isinstance(mod, torch.nn.Conv2d):
+            last = name
+    assert last == ref_model.cam_target()[0] == "levels.2.global_tokenizer.pos_embed"
+    x = torch.zeros(1, 3, 224, 224, device="cuda")
+    with pytest.raises(NotImplementedError):
+        model.forward_cam(x)
+    with pytest.raises(NotImplementedError):
+        with torch.enable_grad():
+            model(x)
