@@ -19,6 +19,9 @@ ACT_NONE, ACT_SILU, ACT_GELU, ACT_RELU = 0, 1, 2, 3
 def _need_gpu():
     assert torch.cuda.is_available() and _lib.lib().b200df_device_count() > 0, "these tests need a B200"
     torch.cuda.set_device(0)
+    # the PyTorch side is the fp32 REFERENCE of each op: no TF32 in its convolutions / matmuls
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
 
 
 def gen(seed):
