@@ -1,9 +1,14 @@
 #!/usr/bin/env python
 """bench.py -- EfficientNet-B0 224x224 eval images/s on N B200s (BASELINE.json metric, configs[1]).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch 256] [--workload eval|cam]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch 256] [--workload eval|cam] [--model NAME]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
     python bench.py --impl reference ...      # the reference's CPU path (oracle port) on the host cores
+
+The default line is BASELINE.json's headline (configs[1]); it also carries, as EXTRA keys measured in the same run:
+`cam` (configs[2]: Grad-CAM batch 64, maps/s), `models` (configs[3], [4]: EfficientFormerV2-S1 and FasterViT-0 batch-256
+eval), `strong` (global batch 256 split over the N GPUs), `latency_n1_ms` / `small_batch` (CUDA-graph replay),
+`sustained` (>= 2 s of steps), `fp32` (the strict path).  `--model` makes any served model the headline of its own line.
 
 One "step" = one pass of the hot path (`logits = model(images)`, orchestrator.py:587-592, plus the
 softmax/argmax pack) over one synthetic batch of `--batch` images per GPU.  Prints ONE JSON line:
@@ -39,6 +44,34 @@ UNIT = "images/s"
 ALGO_MB_PER_IMG = 27.87
 WEIGHT_MB = 8.0
 
+# served model -> (oracle module, oracle class factory) for the CPU legs, and how BASELINE.json refers to it
+MODELS = {
+    "efficientnet_b0": "BASELINE.json configs[1]",
+    "efficientnet_b3": "reference registry default, efficientnet_pytorch layout; SURVEY 8f-2",
+    "efficientformerv2_s1": "BASELINE.json configs[3]",
+    "faster_vit_0_224": "BASELINE.json configs[4]",
+    "faster_vit_2_224": "reference registry default `faster_vit` entry; SURVEY 8f-2",
+}
+
+
+def oracle_for(arch: str):
+    """The fp32 CPU restatement of `arch` (cpu_baseline / reference arm only: the checker, never the product)."""
+    if arch == "efficientnet_b3":
+        from oracle.effnet_b3 import EfficientNetB3Oracle
+        return EfficientNetB3Oracle(2)
+    if arch == "efficientformerv2_s1":
+        from oracle.efficientformerv2 import EfficientFormerV2Oracle
+        return EfficientFormerV2Oracle(2)
+    if arch.startswith("faster_vit"):
+        from oracle.fastervit import FasterViTOracle
+        return FasterViTOracle(2, arch)
+    from oracle.effnet_b0 import EfficientNetB0Oracle
+    return EfficientNetB0Oracle(2)
+
+
+def oracle_file(arch: str) -> str:
+    return {"efficientnet_b0": "effnet_b0", "efficientnet_b3": "effnet_b3", "efficientformerv2_s1": "efficientformerv2"}.get(arch, "fastervit")
+
 
 def parse_args() -> argparse.Namespace:
     ap = argparse.ArgumentParser()
@@ -49,11 +82,13 @@ def parse_args() -> argparse.Namespace:
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--workload", choices=["eval", "cam"], default="eval")
     ap.add_argument("--precision", choices=["bf16", "fp32"], default="bf16")
-    ap.add_argument("--model", choices=["efficientnet_b0", "efficientnet_b3"], default="efficientnet_b0",
-                    help="efficientnet_b0 = BASELINE.json's headline (timm layout); efficientnet_b3 = the reference "
-                         "registry's default entry (efficientnet_pytorch layout, SURVEY 8f-2), an extra line")
+    ap.add_argument("--model", choices=sorted(MODELS), default="efficientnet_b0",
+                    help="efficientnet_b0 = BASELINE.json's headline (timm layout, configs[1]); efficientformerv2_s1 / "
+                         "faster_vit_0_224 = configs[3] / [4]; efficientnet_b3 / faster_vit_2_224 = the reference "
+                         "registry's own entries (SURVEY 8f-2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extra keys (cam, models, strong, latency, ...)")
     return ap.parse_args()
 
 
@@ -120,6 +155,11 @@ def synth_state(model, seed: int = 0) -> None:
                 m.running_var.copy_(torch.rand(c, generator=g) + 0.5)
                 m.weight.copy_(torch.rand(c, generator=g) + 0.5)
                 m.bias.copy_(torch.randn(c, generator=g) * 0.1)
+        for name, p in model.named_parameters():   # LayerScale 1e-5 / zero attention biases would hide whole branches
+            if name.endswith(".gamma"):
+                p.copy_(torch.rand(p.shape, generator=g) * 0.4 + 0.1)
+            elif name.endswith("attention_biases"):
+                p.copy_(torch.randn(p.shape, generator=g))
 
 
 _CLASS_KERNEL = {"dw": "dwconv", "expand": "pwconv_tc_kernel<0, 1, 0>", "project": "pwconv_tc_kernel<1", "stem": "stem_tc",
@@ -154,16 +194,18 @@ def peaks() -> tuple[dict, str]:
 
 
 def cpu_eval_images_per_s(state: dict, batch: int, steps: int, warmup: int, seed: int = 0,
-                          arch: str = "efficientnet_b0"):
+                          arch: str = "efficientnet_b0", channels_last: bool = False):
     """The reference eval-loop body (orchestrator.py:587-592) on the fp32 oracle port, host cores."""
     import torch
-    from oracle.effnet_b0 import EfficientNetB0Oracle  # the checker: cpu_baseline / reference arm only
-    from oracle.effnet_b3 import EfficientNetB3Oracle
 
-    model = (EfficientNetB3Oracle(2) if arch == "efficientnet_b3" else EfficientNetB0Oracle(2)).eval()
+    torch.set_num_threads(os.cpu_count() or 1)   # torch.distributed.run exports OMP_NUM_THREADS=1: undo it for the CPU arm
+    model = oracle_for(arch).eval()
     model.load_state_dict(state, strict=False)
     g = torch.Generator().manual_seed(seed)
     x = torch.randn(batch, 3, 224, 224, generator=g)
+    if channels_last:   # what the reference's trainers use (trainers/efficientnet.py:250-252); second reported row
+        model = model.to(memory_format=torch.channels_last)
+        x = x.contiguous(memory_format=torch.channels_last)
     times = []
     with torch.inference_mode():
         for i in range(warmup + steps):
@@ -180,17 +222,16 @@ def cpu_eval_images_per_s(state: dict, batch: int, steps: int, warmup: int, seed
 
 def run_reference(args) -> None:
     """--impl reference: the reference's own CPU path for this metric.  The reference's arithmetic
-    lives in timm (absent, not installable here), so this is the oracle port (kind "port")."""
+    lives in timm / efficientnet_pytorch / fastervit (absent, not installable here), so this is the oracle port
+    (kind "port"), on ALL host cores whatever launcher started us (rank 0 only under torchrun)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
+    from deepfakedetection_b200 import registry
 
-    from deepfakedetection_b200.module import B200EfficientNetB0, B200EfficientNetB3
-
-    m = (B200EfficientNetB3 if args.model == "efficientnet_b3" else B200EfficientNetB0)(2, "fp32")
+    m = registry.get_model_spec(args.model + ".b200_fp32").builder(args.model + ".b200_fp32", 2)
     synth_state(m)
-    sample_batch = 64
+    sample_batch = 64 if args.model.startswith("efficientnet") else 32
     ips, ms, cores = cpu_eval_images_per_s(m.state_dict(), sample_batch, args.steps, min(args.warmup, 3),
                                            arch=args.model)
     line = {
@@ -200,8 +241,8 @@ def run_reference(args) -> None:
         "config": {"workload": f"{args.model} eval forward 224x224, 2-class head, fp32 eager on host cores",
                    "batch_per_step": sample_batch, "torch_threads": cores},
         "cpu_baseline": {"value": round(ips, 2), "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{args.steps} steps x {sample_batch} images, oracle/{args.model.replace('efficientnet', 'effnet')}.py fp32 eager "
-                                   f"(timm not installable; os.cpu_count={os.cpu_count()})"},
+                         "sample": f"{args.steps} steps x {sample_batch} images, oracle/{oracle_file(args.model)}.py fp32 eager "
+                                   f"(third-party model code not installable; os.cpu_count={os.cpu_count()})"},
         "e2e": {"value": round(ips, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -286,24 +327,29 @@ def run_b200(args) -> None:
     with torch.inference_mode():
         for _ in range(W):
             rec = pack_records(step(images), labels)
+        # the collective is part of the timed region: warm it (communicator set-up, first-use buffers) like the kernels
+        for _ in range(2):
+            gather_records(torch.cat([rec] * K, 0), equal_shards=True)
         sync_all()
         # ---- timed region 1: device-resident inputs -> `value` ----
         _lib.reset_launch_count()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0, ev1, evc = (torch.cuda.Event(enable_timing=True) for _ in range(3))
         lo = sampler.mark()
         ev0.record()
         recs = []
         for _ in range(K):
             recs.append(pack_records(step(images), labels))
-        allrec = gather_records(torch.cat(recs, 0))    # the one collective: all-gather of probs/preds/labels
+        evc.record()
+        # the one collective: all-gather of probs/preds/labels (every rank holds K*B records: no size exchange)
+        allrec = gather_records(torch.cat(recs, 0), equal_shards=True)
         ev1.record()
         sync_all()
         hi = sampler.mark()
-        launches = _lib.launch_count() + (2 if world > 1 else 0)
-        ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+        launches = _lib.launch_count() + (1 if world > 1 else 0)
+        ms = torch.tensor([ev0.elapsed_time(ev1), ev0.elapsed_time(evc), evc.elapsed_time(ev1)], device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        ms_total = float(ms.item())
+        ms_total, ms_compute, ms_gather = (float(v) for v in ms.tolist())
         assert allrec.shape[0] == world * K * B
         # keep the clock sampler honest for very short runs
         while rank == 0 and sampler.proc is not None and sampler.mark() - lo < 3 and hi - lo < 3:
@@ -331,6 +377,10 @@ def run_b200(args) -> None:
             a = per_class.setdefault(cls, [0.0, 0.0, 0.0, 0])
             a[0] += t; a[1] += by; a[2] += fl; a[3] += 1
         eng.set_profile(False)
+
+        extras = {}
+        if not args.no_extras and args.model == "efficientnet_b0" and args.workload == "eval" and args.precision == "bf16":
+            extras = run_extras(args, model, images, labels, dev, rank, world, local, sync_all, sampler)
     sampler.stop()
     if world > 1:
         dist.barrier(device_ids=[local])
@@ -339,9 +389,151 @@ def run_b200(args) -> None:
         if world > 1:
             dist.destroy_process_group()
         return
-    finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, sampler.summary(lo, hi), model, e2e_u8)
+    finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, sampler.summary(lo, hi), model, e2e_u8,
+                ms_compute=ms_compute, ms_gather=ms_gather, extras=extras)
     if world > 1:
         dist.destroy_process_group()
+
+
+def timed_steps(fn, k, dev, world, local, warm: int = 3) -> float:
+    """ms for k calls of fn() (CUDA events on the current stream, barrier + sync on both sides, max over ranks)."""
+    import torch
+    import torch.distributed as dist
+
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier(device_ids=[local])
+        torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(k):
+        fn()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def class_table(eng, fn, dev, reps: int = 3):
+    """Per-kernel-class CUDA-event times / algorithmic bytes / flops of one call of fn() (profiling pass)."""
+    import torch
+
+    per = {}
+    eng.set_profile(True)
+    for _ in range(reps):
+        fn()
+    torch.cuda.synchronize(dev)
+    for nm, t, by, fl in eng.profile_records():
+        a = per.setdefault(nm.split(".")[0], [0.0, 0.0, 0.0, 0])
+        a[0] += t; a[1] += by; a[2] += fl; a[3] += 1
+    eng.set_profile(False)
+    return {c: {"ms": round(t / reps, 4), "launches": cnt // reps,
+                "GBps": round(by / t / 1e6, 1) if t > 0 else None, "TFLOPs": round(fl / t / 1e9, 2) if t > 0 else None,
+                "bytes": by / reps, "flops": fl / reps}
+            for c, (t, by, fl, cnt) in per.items()}
+
+
+def roofline_of(table: dict, pk: dict) -> dict:
+    """Dominant class of a per-class table against whichever measured roof (HBM copy rate / dense bf16 rate) it is nearer to."""
+    dom = max(table, key=lambda c: table[c]["ms"])
+    r = table[dom]
+    t = r["ms"] * 1e-3
+    hbm = r["bytes"] / t / 1e9 / float(pk["hbm_gbs"])
+    tens = r["flops"] / t / 1e12 / float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"]))
+    tot = sum(v["ms"] for v in table.values())
+    if tens > hbm:
+        return {"kernel": dom, "bound": "tensor", "achieved": round(r["flops"] / t / 1e12, 1), "unit": "TFLOP/s",
+                "peak": float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"])), "frac": round(tens, 4),
+                "frac_of_hbm": round(hbm, 4), "share_of_step": round(r["ms"] / tot, 3), "launches_per_step": r["launches"]}
+    return {"kernel": dom, "bound": "hbm", "achieved": round(r["bytes"] / t / 1e9, 1), "unit": "GB/s", "peak": float(pk["hbm_gbs"]),
+            "frac": round(hbm, 4), "frac_of_tensor": round(tens, 4), "share_of_step": round(r["ms"] / tot, 3),
+            "launches_per_step": r["launches"]}
+
+
+def run_extras(args, model, images, labels, dev, rank, world, local, sync_all, sampler) -> dict:
+    """Extra keys of the default line (see the module docstring).  Every number: CUDA events, >= 3 warm-ups, max over ranks."""
+    import torch
+
+    from deepfakedetection_b200 import registry
+    from deepfakedetection_b200.evaluate import pack_records
+
+    pk, _ = peaks()
+    out: dict = {}
+    B = images.shape[0]
+
+    # strong scaling: BASELINE configs[1]'s global batch 256 split over the N GPUs (SURVEY 8d); CUDA-graph replay below 65
+    bs = max(1, 256 // world)
+    xs = images[:bs]
+    ms = timed_steps(lambda: pack_records(model(xs), labels[:bs]), 50, dev, world, local)
+    out["strong"] = {"global_batch": bs * world, "batch_per_gpu": bs, "value": round(bs * world * 50 / (ms * 1e-3), 1), "unit": UNIT,
+                     "ms_per_step": round(ms / 50, 4), "cuda_graph": bs <= model._engine.graph_max_n}
+    # the UI's regime: one image (web_ui.py:251-268), and 32 images (8-GPU strong scaling's per-GPU share)
+    x1, x32 = images[:1], images[:32]
+    ms1 = timed_steps(lambda: model(x1), 200, dev, 1, local)
+    out["latency_n1_ms"] = round(ms1 / 200, 4)
+    ms32 = timed_steps(lambda: model(x32), 100, dev, 1, local)
+    out["small_batch"] = {"batch": 32, "value": round(32 * 100 / (ms32 * 1e-3), 1), "unit": UNIT, "ms_per_step": round(ms32 / 100, 4)}
+    keep = model._engine.graph_max_n
+    model._engine.graph_max_n = 0
+    ms1d = timed_steps(lambda: model(x1), 100, dev, 1, local)
+    ms32d = timed_steps(lambda: model(x32), 50, dev, 1, local)
+    model._engine.graph_max_n = keep
+    out["latency_n1_ms_no_graph"] = round(ms1d / 100, 4)
+    out["small_batch"]["ms_per_step_no_graph"] = round(ms32d / 50, 4)
+
+    # >= 2 s of back-to-back steps: the rate once the burst clock is gone
+    lo = sampler.mark()
+    k = max(100, int(2200.0 / max(timed_steps(lambda: model(images), 10, dev, world, local) / 10, 1e-3)))
+    ms = timed_steps(lambda: pack_records(model(images), labels), k, dev, world, local, warm=0)
+    hi = sampler.mark()
+    out["sustained"] = {"steps": k, "seconds": round(ms * 1e-3, 2), "value": round(world * B * k / (ms * 1e-3), 1), "unit": UNIT,
+                        "clocks": sampler.summary(lo, hi) if rank == 0 else None}
+
+    # configs[2]: Grad-CAM, batch 64, one GPU's worth per rank (forward + fused CAM reduction + 224^2 map)
+    x64 = images[:64]
+    ms = timed_steps(lambda: model.forward_cam(x64, None), 50, dev, world, local)
+    cam = {"metric": "efficientnet_b0_gradcam_maps_per_s", "value": round(world * 64 * 50 / (ms * 1e-3), 1), "unit": "maps/s",
+           "batch_per_gpu": 64, "ms_per_step": round(ms / 50, 4), "config": "BASELINE.json configs[2]: forward + fused Grad-CAM, batch 64"}
+    tab = class_table(model._engine, lambda: model.forward_cam(x64, None), dev)
+    cam["kernels"] = {c: {k2: v[k2] for k2 in ("ms", "launches", "GBps")} for c, v in tab.items() if c in ("cam", "cam_upsample", "conv_head", "dw")}
+    out["cam"] = cam
+
+    # strict fp32 path throughput (the <= 1e-3 logit path), batch 256
+    m32 = registry.get_model_spec("efficientnet_b0.b200_fp32").builder("efficientnet_b0.b200_fp32", 2)
+    synth_state(m32)
+    m32.to(dev).eval()
+    ms = timed_steps(lambda: m32(images), 5, dev, world, local)
+    out["fp32"] = {"value": round(world * B * 5 / (ms * 1e-3), 1), "unit": UNIT, "ms_per_step": round(ms / 5, 3)}
+    del m32
+    torch.cuda.empty_cache()
+
+    # configs[3], configs[4]: the other two backbones, bf16 batch 256 per GPU
+    models = {}
+    for name in ("efficientformerv2_s1", "faster_vit_0_224"):
+        m = registry.get_model_spec(name).builder(name, 2)
+        synth_state(m)
+        m.to(dev).eval()
+        ms = timed_steps(lambda: pack_records(m(images), labels), 10, dev, world, local)
+        tab = class_table(m._engine, lambda: m(images), dev)
+        algo_gb = sum(v["bytes"] for v in tab.values()) / 1e9
+        gflop = sum(v["flops"] for v in tab.values()) / 1e9
+        models[name] = {
+            "metric": f"{name}_224_eval_images_per_s", "value": round(world * B * 10 / (ms * 1e-3), 1), "unit": UNIT,
+            "ms_per_step": round(ms / 10, 4), "batch_per_gpu": B, "dtype": "bf16", "config": MODELS[name],
+            "roofline": roofline_of(tab, pk),
+            "net": {"algorithmic_GB_per_step": round(algo_gb, 3), "GFLOP_per_step": round(gflop, 1),
+                    "frac_of_hbm_peak": round(algo_gb / (ms / 10 * 1e-3) / float(pk["hbm_gbs"]), 4),
+                    "frac_of_tensor_peak": round(gflop / 1e3 / (ms / 10 * 1e-3) / float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"])), 4)},
+            "kernels": {c: {k2: v[k2] for k2 in ("ms", "launches", "GBps", "TFLOPs")} for c, v in sorted(tab.items(), key=lambda kv: -kv[1]["ms"])},
+        }
+        del m
+        torch.cuda.empty_cache()
+    out["models"] = models
+    return out
 
 
 def run_e2e(model, step, B, K, W, dev, rank, world, local, u8: bool = False):
@@ -411,7 +603,8 @@ def emit(line: dict) -> None:
         os.write(_JSON_FD, text.encode())
 
 
-def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, clocks, model, e2e_u8=None) -> None:
+def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, clocks, model, e2e_u8=None,
+                ms_compute=None, ms_gather=None, extras=None) -> None:
     import torch
 
     pk, pk_kind = peaks()
@@ -430,12 +623,18 @@ def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, 
     hbm_peak = float(pk["hbm_gbs"])
     achieved = by / cnt / t_launch / 1e9
     traffic, traffic_src = ncu_traffic_per_launch(dom) if args.model == "efficientnet_b0" else (None, None)  # ncu capture is B0's
+    tens_peak = float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"]))
+    tens_frac = fl / cnt / t_launch / 1e12 / tens_peak
     roofline = {"kernel": dom, "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
                 "frac": round(achieved / hbm_peak, 4), "traffic": None if traffic is None else round(traffic),
                 "traffic_source": traffic_src, "algorithmic_bytes_per_launch": round(by / cnt),
                 "peak_source": f"{pk_kind} (MEASURED_PEAKS.json hbm_gbs)",
                 "share_of_step": round(t / reps / prof_ms, 3), "launches_per_step": cnt // reps,
-                "avg_launch_ms": round(t_launch * 1e3, 4)}
+                "avg_launch_ms": round(t_launch * 1e3, 4), "frac_of_tensor": round(tens_frac, 4)}
+    if tens_frac > achieved / hbm_peak:   # a tensor-pipe-bound dominant kernel (FasterViT's dense 3x3 convs / MLP GEMMs)
+        roofline.update({"bound": "tensor", "achieved": round(fl / cnt / t_launch / 1e12, 1), "peak": tens_peak, "unit": "TFLOP/s",
+                         "frac": round(tens_frac, 4), "frac_of_hbm": round(achieved / hbm_peak, 4),
+                         "peak_source": f"{pk_kind} (MEASURED_PEAKS.json bf16_tflops_sustained)"})
     es = 2 if args.precision == "bf16" else 4
     algo_gb = (ALGO_MB_PER_IMG * (es / 2) * B + WEIGHT_MB * (es / 2)) / 1e3
     if args.model != "efficientnet_b0":  # sum of the per-launch algorithmic bytes the engine tags its launches with
@@ -448,25 +647,33 @@ def finish_line(args, world, B, K, W, ms_total, launches, e2e, per_class, reps, 
         "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": args.precision, "data": "synthetic",
         "config": {"workload": (f"{args.model} eval forward" if args.workload == "eval" else f"{args.model} forward + fused Grad-CAM")
-                   + " 224x224, 2-class head" + (" (BASELINE.json configs[1])" if args.model == "efficientnet_b0" else
-                                                 " (reference registry default, efficientnet_pytorch layout; SURVEY 8f-2)"), "batch_per_gpu": B, "global_batch": B * world,
+                   + " 224x224, 2-class head (" + MODELS[args.model] + ")", "batch_per_gpu": B, "global_batch": B * world,
                    "input": "float32 NCHW [B,3,224,224] resident in HBM", "l2": "inputs (154 MB/batch) and per-step "
                    "activations (>3 GB) exceed the 126 MB L2; no explicit flush",
-                   "collective": "one all_gather of packed probs/preds/labels after the K steps (inside the timed region)",
+                   "collective": "one all_gather of packed probs/preds/labels after the K steps (inside the timed region, warmed)",
                    "weights": "random init + randomised BN (synthetic)"},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_net": net, "kernels": table,
     }
+    if ms_compute is not None:
+        line["compute_ms_per_step"] = round(ms_compute / K, 4)
+        line["gather_ms"] = round(ms_gather, 4)
     if e2e is not None:
         line["e2e"] = e2e
     if e2e_u8 is not None:  # extra, not the headline: same metric fed with uint8 crops (4x fewer PCIe bytes)
         line["e2e_u8"] = e2e_u8
     if not args.no_cpu_baseline and world == 1:  # rank 0 at N=1 only
-        steps_cpu = 6
-        ips, ms, cores = cpu_eval_images_per_s({k: v.cpu() for k, v in model.state_dict().items()}, 64, steps_cpu, 2,
-                                               arch=args.model)
+        steps_cpu = 6 if args.model.startswith("efficientnet") else 3
+        bs_cpu = 64 if args.model.startswith("efficientnet") else 32
+        state = {k: v.cpu() for k, v in model.state_dict().items()}
+        ips, ms, cores = cpu_eval_images_per_s(state, bs_cpu, steps_cpu, 2, arch=args.model)
         line["cpu_baseline"] = {"value": round(ips, 2), "unit": UNIT, "cores": cores, "kind": "port",
-                                "sample": f"{steps_cpu} timed steps x 64 images (+2 warm-up), oracle/{args.model.replace('efficientnet', 'effnet')}.py fp32 eager, "
+                                "sample": f"{steps_cpu} timed steps x {bs_cpu} images (+2 warm-up), oracle/{oracle_file(args.model)}.py fp32 eager, "
                                           f"torch threads={cores}, os.cpu_count={os.cpu_count()}"}
+        if args.model == "efficientnet_b0":  # BASELINE.md section 2's second row
+            ips_cl, _, _ = cpu_eval_images_per_s(state, bs_cpu, 4, 1, arch=args.model, channels_last=True)
+            line["cpu_baseline"]["channels_last"] = round(ips_cl, 2)
+    for k2, v in (extras or {}).items():
+        line[k2] = v
     emit(line)
 
 

@@ -6,7 +6,9 @@ arithmetic happens inside ``libb200df.so``.
 
 from __future__ import annotations
 
+import collections
 import ctypes as C
+import os
 import threading
 
 import torch
@@ -51,8 +53,14 @@ class Engine:
         _lib.check(self._lib.b200df_feature_shape(self._h, C.byref(ch), C.byref(side)))
         self.feature_channels, self.feature_side = int(ch.value), int(side.value)  # Grad-CAM activation A
         self.precision: int | None = None
-        self._ws: dict[int, tuple[torch.Tensor, int, int]] = {}
+        # workspaces keyed by (batch size, stream): two forwards of the same n on different streams never share scratch
+        self._ws: "collections.OrderedDict[tuple[int, int], tuple[torch.Tensor, int, int]]" = collections.OrderedDict()
         self._lock = threading.Lock()
+        # CUDA-graph replay for small batches (launch-bound regime: the UI's n = 1, strong scaling's 32 images per GPU):
+        # one graph per batch size, captured on first use; B200DF_GRAPH_MAX_N=0 disables it
+        self.graph_max_n = int(os.environ.get("B200DF_GRAPH_MAX_N", "64"))
+        self._graphs: dict[int, tuple[torch.cuda.CUDAGraph, torch.Tensor, torch.Tensor]] = {}
+        self._profiling = False
 
     # -- description ---------------------------------------------------------------------------------
     def expected_tensors(self) -> list[tuple[str, int]]:
@@ -78,20 +86,33 @@ class Engine:
             with torch.cuda.device(self.device):
                 _lib.check(self._lib.b200df_finalize(self._h, precision))
             self.precision = precision
-            self._ws.clear()
+            self._drop_workspaces()
 
     # -- workspace -----------------------------------------------------------------------------------
-    def _workspace(self, n: int) -> tuple[int, int]:
-        hit = self._ws.get(n)
+    def _drop_workspaces(self) -> None:
+        cur = torch.cuda.current_stream(self.device)
+        for buf, _base, _size in self._ws.values():
+            buf.record_stream(cur)   # kernels launched on another stream may still be using it
+        self._ws.clear()
+        self._graphs.clear()
+
+    def _workspace(self, n: int, stream_id: int | None = None) -> tuple[int, int]:
+        if stream_id is None:
+            stream_id = torch.cuda.current_stream(self.device).cuda_stream
+        key = (n, stream_id)
+        hit = self._ws.get(key)
         if hit is None:
             need = C.c_size_t()
             _lib.check(self._lib.b200df_workspace_bytes(self._h, n, 1, C.byref(need)))
             buf = torch.empty(int(need.value) + _ALIGN, dtype=torch.uint8, device=self.device)
             base = (buf.data_ptr() + _ALIGN - 1) // _ALIGN * _ALIGN
-            if len(self._ws) >= 4:  # keep a few batch sizes (full batch, ragged tail, n=1 from the UI)
-                self._ws.pop(next(iter(self._ws)))
+            while len(self._ws) >= 6:  # a few (batch size, stream) pairs: full batch, ragged tail, n = 1 from the UI ...
+                _k, (old, _b, _s) = self._ws.popitem(last=False)   # least recently used
+                old.record_stream(torch.cuda.current_stream(self.device))
             hit = (buf, base, int(need.value))
-            self._ws[n] = hit
+            self._ws[key] = hit
+        else:
+            self._ws.move_to_end(key)
         return hit[1], hit[2]
 
     # -- hot path ------------------------------------------------------------------------------------
@@ -103,10 +124,52 @@ class Engine:
         if n == 0:
             return logits
         with self._lock, torch.cuda.device(images.device):
+            if 0 < n <= self.graph_max_n and not self._profiling and not torch.cuda.is_current_stream_capturing():
+                if self._forward_graphed(images, logits):
+                    return logits
             base, size = self._workspace(n)
             _lib.check(self._lib.b200df_forward(self._h, _ptr(images), n, _ptr(logits), C.c_void_p(base), size,
                                                _stream_ptr(images.device)))
         return logits
+
+    def _forward_graphed(self, images: torch.Tensor, logits: torch.Tensor) -> bool:
+        """Replay (capturing on first use) the CUDA graph of one n-image forward: ~70-300 launches become one.
+        Returns False (and switches graphs off) if capture is not possible on this driver."""
+        n = images.shape[0]
+        hit = self._graphs.get(n)
+        if hit is None:
+            try:
+                cur = torch.cuda.current_stream(self.device)
+                side = torch.cuda.Stream(self.device)
+                with torch.inference_mode(False):   # the static buffers outlive the caller's inference_mode block
+                    x = torch.empty(images.shape, dtype=images.dtype, device=images.device)
+                    y = torch.empty(logits.shape, dtype=logits.dtype, device=logits.device)
+                base, size = self._workspace(n, stream_id=-n)   # scratch owned by this graph
+                side.wait_stream(cur)
+                with torch.cuda.stream(side):
+                    x.copy_(images)
+                    # un-captured warm-up: encodes the tensor maps / tile plans of this (n, workspace) on the host
+                    _lib.check(self._lib.b200df_forward(self._h, _ptr(x), n, _ptr(y), C.c_void_p(base), size,
+                                                       _stream_ptr(self.device)))
+                side.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=side):
+                    _lib.check(self._lib.b200df_forward(self._h, _ptr(x), n, _ptr(y), C.c_void_p(base), size,
+                                                       _stream_ptr(self.device)))
+                cur.wait_stream(side)
+                hit = (g, x, y)
+                self._graphs[n] = hit
+            except Exception as ex:  # noqa: BLE001 - capture is an optimisation, never a requirement
+                import warnings
+
+                warnings.warn(f"b200 backend: CUDA-graph capture failed ({ex}); small batches take the direct path", stacklevel=2)
+                self.graph_max_n = 0
+                return False
+        g, x, y = hit
+        x.copy_(images, non_blocking=True)
+        g.replay()
+        logits.copy_(y, non_blocking=True)
+        return True
 
     def forward_u8(self, images_hwc: torch.Tensor, mean, std) -> torch.Tensor:
         if not images_hwc.is_cuda or images_hwc.dtype != torch.uint8:
@@ -184,6 +247,7 @@ class Engine:
 
     # -- per-launch profiling (bench.py) -----------------------------------------------------------------
     def set_profile(self, enable: bool) -> None:
+        self._profiling = bool(enable)
         _lib.check(self._lib.b200df_set_profile(self._h, 1 if enable else 0))
 
     def profile_records(self) -> list[tuple[str, float, float, float]]:

@@ -84,13 +84,18 @@ def pack_records(logits: torch.Tensor, labels: torch.Tensor | None) -> torch.Ten
     return out
 
 
-def gather_records(local: torch.Tensor, group=None) -> torch.Tensor:
+def gather_records(local: torch.Tensor, group=None, equal_shards: bool = False) -> torch.Tensor:
     """All-gather variable-length [n_r, W] record blocks into rank order [sum n_r, W] (one collective
-    for the sizes, one for the payload).  Works on CUDA/NCCL and CPU/gloo."""
+    for the sizes, one for the payload).  Works on CUDA/NCCL and CPU/gloo.  ``equal_shards=True`` (every rank holds
+    the same number of records, e.g. fixed per-GPU batches) skips the size exchange and its host sync: ONE collective."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return local
     world = dist.get_world_size(group)
     width = local.shape[1]
+    if equal_shards:
+        gathered = torch.empty((world * local.shape[0], width), dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(gathered, local.contiguous(), group=group)
+        return gathered
     sizes = torch.zeros(world, dtype=torch.int64, device=local.device)
     mine = torch.tensor([local.shape[0]], dtype=torch.int64, device=local.device)
     dist.all_gather_into_tensor(sizes, mine, group=group)

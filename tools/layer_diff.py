@@ -68,6 +68,9 @@ def reference_tensors(oracle, x: torch.Tensor) -> dict[str, torch.Tensor]:
 def main(name: str = "efficientformerv2_s1", precision: str = "fp32", n: int = 2, thresh: float | None = None) -> int:
     from oracle.effnet_b0 import synth_images
 
+    import os
+
+    os.environ["B200DF_GRAPH_MAX_N"] = "0"   # every forward must really run (and stop where asked), not replay a graph
     lib = _lib.lib()
     oracle = oracle_for(name)
     x = synth_images(n, seed=5)
@@ -102,7 +105,7 @@ def main(name: str = "efficientformerv2_s1", precision: str = "fp32", n: int = 2
             model(xg)
         torch.cuda.synchronize()
         nseq = r.numel() // (rows * c)
-        ws_buf = eng._ws[n][0]                       # the uint8 workspace tensor behind `ws_base`
+        ws_buf = next(v[0] for k, v in eng._ws.items() if k[0] == n and v[1] == ws_base)   # the uint8 tensor behind `ws_base`
         o = ws_base - ws_buf.data_ptr() + off.value
         t = ws_buf[o:o + nseq * seq_rows * c * es].view(dt)
         got = t.view(nseq, seq_rows, c)[:, row_off:row_off + rows].float().cpu()

@@ -47,7 +47,13 @@ def step(path: str) -> None:
             ("sm__warps_active.avg.pct_of_peak_sustained_active", "occ%", 6),
             ("sm__inst_executed_pipe_tensor.avg.pct_of_peak_sustained_active", "tens%", 6),
             ("launch__registers_per_thread", "regs", 5), ("launch__grid_size", "grid", 6), ("launch__block_size", "blk", 5)]
-    print("# one forward step (N=256, bf16), ncu --set full --clock-control none; dram bytes are per launch")
+    # the tensor-pipe column: whichever sm__pipe_tensor* / sm__inst_executed_pipe_tensor* percentage this ncu version exports
+    tens = [h for h in hdr if "pipe_tensor" in h and "pct_of_peak" in h]
+    tens = [h for h in tens if "cycles_active" in h] or tens
+    if tens:
+        cols = [(tens[0], c[1], c[2]) if c[1] == "tens%" else c for c in cols]
+    print("# one forward step (N=256, bf16), ncu --set full --clock-control none; dram bytes are per launch"
+          + (f"; tens% = {tens[0]}" if tens else ""))
     print(f"{'#':>3s} {'kernel':44s} " + " ".join(f"{c[1]:>{c[2]}s}" for c in cols))
     for n, r in enumerate(data):
         if len(r) < len(hdr):
