@@ -13,6 +13,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <stdlib.h>
+
 namespace b200df {
 
 constexpr int kAttnThreads = 256;
@@ -189,6 +191,14 @@ static cudaError_t attn_launch(const AttnArgs& a, cudaStream_t s) {
 
 cudaError_t launch_attention(const AttnArgs& a, int dtype, cudaStream_t s) {
   if (a.nseq <= 0) return cudaSuccess;
+  if (dtype == kBF16) {   // tensor-core kernel (attn_mma.cu) for the shapes it is built for; B200DF_GEMM=simt / B200DF_ATTN=simt: this one
+    const char* e1 = getenv("B200DF_ATTN");
+    const char* e2 = getenv("B200DF_GEMM");
+    if (!((e1 && e1[0] == 's') || (e2 && e2[0] == 's'))) {
+      const cudaError_t e = launch_attention_mma(a, s);
+      if (e != cudaErrorNotSupported) return e;
+    }
+  }
   const bool th = a.th1_w != nullptr;
   if (a.dk % 8 || a.dv % 8 || a.heads > kAttnMaxHeads || a.heads < 1 || a.nq < 1 || a.nk < 1) return cudaErrorInvalidValue;
   if (a.q_pitch % 8 || a.k_pitch % 8 || a.v_pitch % 8 || a.q_off % 8 || a.k_off % 8 || a.v_off % 8) return cudaErrorInvalidValue;

@@ -1,0 +1,379 @@
+// Small-sequence multi-head attention on the tensor cores (bf16 path), one CTA per sequence, eight warps.
+//   S = (q k^T) * scale + bias;  [talking_head1];  P = softmax_j(S);  [talking_head2];  out = P v (+ v_local); [GELU]
+// Same contract as attn.cu (the fp32 / any-shape CUDA-core kernel): replaces timm EfficientFormerV2 `Attention2d` /
+// `Attention2dDownsample` and fastervit `WindowAttention` inside the reference's `model(images)`
+// (/root/reference/orchestration/orchestrator.py:590).
+//
+// Why warp-level MMA (mma.sync m16n8k16, bf16 x bf16 -> fp32) and not a tcgen05 tile: a sequence is 16-53 queries by
+// 16-196 keys per head with d = 16-128 -- one 128-row UMMA tile would hold 2.4-8 sequences of DIFFERENT keys, i.e. mostly
+// masked cross terms, and the probabilities would have to leave TMEM, be re-laid out as a shared-memory operand and come
+// back between the two products.  With register-resident fragments the whole (head, 16-query block) unit is one warp's
+// work, flash-attention style: the S accumulators of two adjacent 8-key tiles ARE the A fragment of the P.V product, the
+// softmax is two quad shuffles per row, and nothing but q, k, v is read and nothing but `out` is written.
+//   * staging (per pass of `hp` heads): K rows as they are ([key][d], pitch d+8 -> conflict-free 32-bit B-fragment loads),
+//     V TRANSPOSED ([d][key], pitch keys+8) so that the P.V B fragment is a 32-bit load too; pads are zeroed;
+//   * Q fragments come straight from global memory (L2-hot GEMM output), the bias table from L2;
+//   * talking heads (EfficientFormerV2) couple the heads between the two products: S of all heads goes to shared memory in
+//     fp32, the two 8x8 mixes and the softmax run there (as in attn.cu), and the P.V A fragments are built from it.
+#include "common.cuh"
+#include "kernels.h"
+
+#include <algorithm>
+
+namespace b200df {
+
+namespace {
+
+constexpr int kMmaThreads = 256;
+constexpr int kMmaWarps = 8;
+
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+template <int DK, int DV, int NKT>
+struct AttnGeom {
+  static constexpr int NK8 = NKT * 8;                 // keys padded to whole 8-key S tiles
+  static constexpr int NKP = (NK8 + 15) / 16 * 16;    // keys padded to whole 16-key P.V steps
+  static constexpr int KP = DK + 8;                   // K row pitch (bf16 elements)
+  static constexpr int VP = NKP + 8;                  // V^T row pitch
+  static constexpr int SP = NKP + 8;                  // fp32 score row pitch (talking-head path)
+  static constexpr size_t k_bytes(int heads, int nk) { return (size_t)heads * ((nk + 7) / 8 * 8) * KP * 2; }
+  static constexpr size_t v_bytes(int heads) { return (size_t)heads * DV * VP * 2; }
+};
+
+// ---- staging ---------------------------------------------------------------------------------------------------
+template <int DK, int DV, int NKT>
+__device__ __forceinline__ void stage_k(const AttnArgs& a, int seq, int h0, int nh, bf16* Ks) {
+  using G = AttnGeom<DK, DV, NKT>;
+  const bf16* k = reinterpret_cast<const bf16*>(a.k);
+  const int rows = G::NK8;
+  for (int idx = threadIdx.x; idx < nh * rows * (DK / 8); idx += kMmaThreads) {
+    const int c8 = idx % (DK / 8);
+    const int r = idx / (DK / 8);
+    const int j = r % rows, hl = r / rows;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (j < a.nk)
+      v = __ldg(reinterpret_cast<const uint4*>(k + ((size_t)seq * a.nk + j) * a.k_pitch + a.k_off + (h0 + hl) * DK + c8 * 8));
+    *reinterpret_cast<uint4*>(Ks + ((size_t)hl * rows + j) * G::KP + c8 * 8) = v;
+  }
+}
+
+template <int DK, int DV, int NKT>
+__device__ __forceinline__ void stage_vt(const AttnArgs& a, int seq, int h0, int nh, bf16* Vt) {
+  using G = AttnGeom<DK, DV, NKT>;
+  const bf16* v = reinterpret_cast<const bf16*>(a.v);
+  for (int idx = threadIdx.x; idx < nh * G::NKP * (DV / 8); idx += kMmaThreads) {
+    const int c8 = idx % (DV / 8);
+    const int r = idx / (DV / 8);
+    const int j = r % G::NKP, hl = r / G::NKP;
+    uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+    if (j < a.nk)
+      raw = __ldg(reinterpret_cast<const uint4*>(v + ((size_t)seq * a.nk + j) * a.v_pitch + a.v_off + (h0 + hl) * DV + c8 * 8));
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+    bf16* dst = Vt + ((size_t)hl * DV + c8 * 8) * G::VP + j;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      reinterpret_cast<uint16_t*>(dst)[(2 * e) * G::VP] = (uint16_t)(w[e] & 0xffffu);
+      reinterpret_cast<uint16_t*>(dst)[(2 * e + 1) * G::VP] = (uint16_t)(w[e] >> 16);
+    }
+  }
+}
+
+// ---- S = q k^T for one (head, 16-query block): s[NKT][4] in the mma C layout -------------------------------------------
+template <int DK, int DV, int NKT>
+__device__ __forceinline__ void qk_unit(const AttnArgs& a, int seq, int h, int r0, const bf16* Kh, float (&s)[NKT][4]) {
+  using G = AttnGeom<DK, DV, NKT>;
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const bf16* q = reinterpret_cast<const bf16*>(a.q);
+#pragma unroll
+  for (int jt = 0; jt < NKT; ++jt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) s[jt][e] = 0.f;
+  const int i0 = r0 + g, i1 = r0 + g + 8;
+  const bf16* q0 = q + ((size_t)seq * a.nq + min(i0, a.nq - 1)) * a.q_pitch + a.q_off + h * DK;
+  const bf16* q1 = q + ((size_t)seq * a.nq + min(i1, a.nq - 1)) * a.q_pitch + a.q_off + h * DK;
+#pragma unroll
+  for (int ks = 0; ks < DK / 16; ++ks) {
+    uint32_t af[4];
+    af[0] = i0 < a.nq ? __ldg(reinterpret_cast<const uint32_t*>(q0 + ks * 16 + 2 * t)) : 0u;
+    af[1] = i1 < a.nq ? __ldg(reinterpret_cast<const uint32_t*>(q1 + ks * 16 + 2 * t)) : 0u;
+    af[2] = i0 < a.nq ? __ldg(reinterpret_cast<const uint32_t*>(q0 + ks * 16 + 2 * t + 8)) : 0u;
+    af[3] = i1 < a.nq ? __ldg(reinterpret_cast<const uint32_t*>(q1 + ks * 16 + 2 * t + 8)) : 0u;
+#pragma unroll
+    for (int jt = 0; jt < NKT; ++jt) {
+      const bf16* kr = Kh + (size_t)(jt * 8 + g) * G::KP + ks * 16 + 2 * t;
+      mma_bf16_16816(s[jt], af, *reinterpret_cast<const uint32_t*>(kr), *reinterpret_cast<const uint32_t*>(kr + 8));
+    }
+  }
+}
+
+// ---- out = P v for one (head, 16-query block); P given as A fragments per 16-key step ------------------------------------
+template <int DK, int DV, int NKT, typename AFrag>
+__device__ __forceinline__ void pv_unit(const AttnArgs& a, int seq, int h, int r0, const bf16* Vh, AFrag afrag, float inv0,
+                                        float inv1) {
+  using G = AttnGeom<DK, DV, NKT>;
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  float o[DV / 8][4];
+#pragma unroll
+  for (int dt = 0; dt < DV / 8; ++dt)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o[dt][e] = 0.f;
+#pragma unroll
+  for (int kt = 0; kt < G::NKP / 16; ++kt) {
+    uint32_t af[4];
+    afrag(kt, af);
+#pragma unroll
+    for (int dt = 0; dt < DV / 8; ++dt) {
+      const bf16* vr = Vh + (size_t)(dt * 8 + g) * G::VP + kt * 16 + 2 * t;
+      mma_bf16_16816(o[dt], af, *reinterpret_cast<const uint32_t*>(vr), *reinterpret_cast<const uint32_t*>(vr + 8));
+    }
+  }
+  const int oc = a.heads * DV;
+  bf16* out = reinterpret_cast<bf16*>(a.out);
+  const bf16* vl = reinterpret_cast<const bf16*>(a.vlocal);
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const int i = r0 + g + 8 * half;
+    if (i >= a.nq) continue;
+    const float inv = half ? inv1 : inv0;
+    const size_t base = ((size_t)seq * a.nq + i) * oc + h * DV + 2 * t;
+#pragma unroll
+    for (int dt = 0; dt < DV / 8; ++dt) {
+      float x0 = o[dt][2 * half] * inv, x1 = o[dt][2 * half + 1] * inv;
+      if (vl) {
+        const uint32_t l = __ldg(reinterpret_cast<const uint32_t*>(vl + base + dt * 8));
+        x0 += __uint_as_float(l << 16);
+        x1 += __uint_as_float(l & 0xffff0000u);
+      }
+      x0 = apply_act<true>(x0, a.act);
+      x1 = apply_act<true>(x1, a.act);
+      *reinterpret_cast<uint32_t*>(out + base + dt * 8) = pack_bf16x2(x0, x1);
+    }
+  }
+}
+
+// ---- no talking heads: everything between the two products stays in registers -----------------------------------------------
+template <int DK, int DV, int NKT>
+__global__ void __launch_bounds__(kMmaThreads)
+attn_mma_kernel(const AttnArgs a, int hp) {
+  using G = AttnGeom<DK, DV, NKT>;
+  extern __shared__ __align__(16) uint8_t sm[];
+  bf16* Ks = reinterpret_cast<bf16*>(sm);
+  bf16* Vt = reinterpret_cast<bf16*>(sm + G::k_bytes(hp, G::NK8));
+  const int seq = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int RB = (a.nq + 15) / 16;
+  griddep_wait();
+  griddep_launch_dependents();
+  for (int h0 = 0; h0 < a.heads; h0 += hp) {
+    const int nh = min(hp, a.heads - h0);
+    __syncthreads();   // the previous pass is done with the staged tiles
+    stage_k<DK, DV, NKT>(a, seq, h0, nh, Ks);
+    stage_vt<DK, DV, NKT>(a, seq, h0, nh, Vt);
+    __syncthreads();
+    for (int u = warp; u < nh * RB; u += kMmaWarps) {
+      const int hl = u / RB, r0 = (u - hl * RB) * 16, h = h0 + hl;
+      float s[NKT][4];
+      qk_unit<DK, DV, NKT>(a, seq, h, r0, Ks + (size_t)hl * G::NK8 * G::KP, s);
+      // scale + bias, key mask, row max / sum (two rows per thread: g and g + 8; a row lives in one quad)
+      float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+      for (int jt = 0; jt < NKT; ++jt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = r0 + g + 8 * (e >> 1), j = jt * 8 + 2 * t + (e & 1);
+          float v = -INFINITY;
+          if (j < a.nk) {
+            v = s[jt][e] * a.scale;
+            if (a.bias && i < a.nq) v += __ldg(a.bias + ((size_t)h * a.nq + i) * a.nk + j);
+          }
+          s[jt][e] = v;
+          mx[e >> 1] = fmaxf(mx[e >> 1], v);
+        }
+      float sum[2] = {0.f, 0.f};
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+        mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+      }
+#pragma unroll
+      for (int jt = 0; jt < NKT; ++jt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float p = __expf(s[jt][e] - mx[e >> 1]);   // exp(-inf) = 0 for the masked keys
+          s[jt][e] = p;
+          sum[e >> 1] += p;
+        }
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        sum[r] += __shfl_xor_sync(0xffffffffu, sum[r], 1);
+        sum[r] += __shfl_xor_sync(0xffffffffu, sum[r], 2);
+      }
+      auto afrag = [&](int kt, uint32_t (&af)[4]) {   // C fragments of S tiles 2kt, 2kt+1 = A fragment of key step kt
+        af[0] = pack_bf16x2(s[2 * kt][0], s[2 * kt][1]);
+        af[1] = pack_bf16x2(s[2 * kt][2], s[2 * kt][3]);
+        if (2 * kt + 1 < NKT) {
+          af[2] = pack_bf16x2(s[2 * kt + 1][0], s[2 * kt + 1][1]);
+          af[3] = pack_bf16x2(s[2 * kt + 1][2], s[2 * kt + 1][3]);
+        } else {
+          af[2] = 0u;
+          af[3] = 0u;
+        }
+      };
+      pv_unit<DK, DV, NKT>(a, seq, h, r0, Vt + (size_t)hl * DV * G::VP, afrag, 1.0f / sum[0], 1.0f / sum[1]);
+    }
+  }
+}
+
+// ---- talking heads (EfficientFormerV2 Attention2d): scores of ALL heads meet in shared memory between the products ---------
+template <int DK, int DV, int NKT>
+__global__ void __launch_bounds__(kMmaThreads)
+attn_mma_th_kernel(const AttnArgs a, int hp) {
+  using G = AttnGeom<DK, DV, NKT>;
+  extern __shared__ __align__(16) uint8_t sm[];
+  const int H = a.heads, nq = a.nq, nk = a.nk;
+  float* S = reinterpret_cast<float*>(sm);                                        // [H][nq][SP] fp32
+  uint8_t* region = sm + (((size_t)H * nq * G::SP * sizeof(float) + 15) & ~size_t(15));
+  bf16* Ks = reinterpret_cast<bf16*>(region);                                      // all heads (scores phase)
+  bf16* Vt = reinterpret_cast<bf16*>(region);                                      // hp heads at a time (output phase)
+  const int seq = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int RB = (nq + 15) / 16;
+  griddep_wait();
+  griddep_launch_dependents();
+  // ---- scores ----
+  stage_k<DK, DV, NKT>(a, seq, 0, H, Ks);
+  __syncthreads();
+  for (int u = warp; u < H * RB; u += kMmaWarps) {
+    const int h = u / RB, r0 = (u - h * RB) * 16;
+    float s[NKT][4];
+    qk_unit<DK, DV, NKT>(a, seq, h, r0, Ks + (size_t)h * G::NK8 * G::KP, s);
+#pragma unroll
+    for (int jt = 0; jt < NKT; ++jt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int i = r0 + g + 8 * (e >> 1), j = jt * 8 + 2 * t + (e & 1);
+        if (i < nq && j < nk) {
+          float v = s[jt][e] * a.scale;
+          if (a.bias) v += __ldg(a.bias + ((size_t)h * nq + i) * nk + j);
+          S[((size_t)h * nq + i) * G::SP + j] = v;
+        }
+      }
+  }
+  // zero the key padding of every row once: it is read as P = 0 by the 16-key steps of the second product
+  for (int idx = threadIdx.x; idx < H * nq * (G::SP - nk); idx += kMmaThreads) {
+    const int r = idx / (G::SP - nk), c = idx - r * (G::SP - nk);
+    S[(size_t)r * G::SP + nk + c] = 0.f;
+  }
+  __syncthreads();
+  // ---- talking head 1, softmax over keys, talking head 2 (as attn.cu) ----
+  for (int pass = 0; pass < 2; ++pass) {
+    const float* w = pass == 0 ? a.th1_w : a.th2_w;
+    const float* b = pass == 0 ? a.th1_b : a.th2_b;
+    for (int idx = threadIdx.x; idx < nq * nk; idx += kMmaThreads) {
+      const int i = idx / nk, j = idx - i * nk;
+      float v[16];
+      for (int h = 0; h < H; ++h) v[h] = S[((size_t)h * nq + i) * G::SP + j];
+      for (int ho = 0; ho < H; ++ho) {
+        float o = __ldg(b + ho);
+        for (int h = 0; h < H; ++h) o = fmaf(__ldg(w + ho * H + h), v[h], o);
+        S[((size_t)ho * nq + i) * G::SP + j] = o;
+      }
+    }
+    __syncthreads();
+    if (pass == 0) {
+      for (int r = warp; r < H * nq; r += kMmaWarps) {
+        float* row = S + (size_t)r * G::SP;
+        float mx = -INFINITY;
+        for (int j = lane; j < nk; j += 32) mx = fmaxf(mx, row[j]);
+        mx = warp_max(mx);
+        float sum = 0.f;
+        for (int j = lane; j < nk; j += 32) {
+          const float e = __expf(row[j] - mx);
+          row[j] = e;
+          sum += e;
+        }
+        const float inv = 1.0f / warp_sum(sum);
+        for (int j = lane; j < nk; j += 32) row[j] *= inv;
+      }
+      __syncthreads();
+    }
+  }
+  // ---- out = P v (+ v_local), hp heads per pass ----
+  for (int h0 = 0; h0 < H; h0 += hp) {
+    const int nh = min(hp, H - h0);
+    __syncthreads();
+    stage_vt<DK, DV, NKT>(a, seq, h0, nh, Vt);
+    __syncthreads();
+    for (int u = warp; u < nh * RB; u += kMmaWarps) {
+      const int hl = u / RB, r0 = (u - hl * RB) * 16, h = h0 + hl;
+      const float* s0 = S + ((size_t)h * nq + min(r0 + g, nq - 1)) * G::SP;
+      const float* s1 = S + ((size_t)h * nq + min(r0 + g + 8, nq - 1)) * G::SP;
+      const bool ok0 = r0 + g < nq, ok1 = r0 + g + 8 < nq;
+      auto afrag = [&](int kt, uint32_t (&af)[4]) {
+        const float2 p00 = *reinterpret_cast<const float2*>(s0 + kt * 16 + 2 * t);
+        const float2 p10 = *reinterpret_cast<const float2*>(s1 + kt * 16 + 2 * t);
+        const float2 p01 = *reinterpret_cast<const float2*>(s0 + kt * 16 + 2 * t + 8);
+        const float2 p11 = *reinterpret_cast<const float2*>(s1 + kt * 16 + 2 * t + 8);
+        af[0] = ok0 ? pack_bf16x2(p00.x, p00.y) : 0u;
+        af[1] = ok1 ? pack_bf16x2(p10.x, p10.y) : 0u;
+        af[2] = ok0 ? pack_bf16x2(p01.x, p01.y) : 0u;
+        af[3] = ok1 ? pack_bf16x2(p11.x, p11.y) : 0u;
+      };
+      pv_unit<DK, DV, NKT>(a, seq, h, r0, Vt + (size_t)hl * DV * G::VP, afrag, 1.0f, 1.0f);
+    }
+  }
+}
+
+template <int DK, int DV, int NKT>
+cudaError_t mma_launch(const AttnArgs& a, bool th, cudaStream_t s) {
+  using G = AttnGeom<DK, DV, NKT>;
+  const size_t budget = th ? 200 * 1024 : 72 * 1024;   // no talking heads: three CTAs per SM
+  const size_t s_bytes = th ? (((size_t)a.heads * a.nq * G::SP * sizeof(float) + 15) & ~size_t(15)) : 0;
+  int hp = a.heads;
+  auto need = [&](int h) {
+    return th ? s_bytes + std::max(G::k_bytes(a.heads, G::NK8), G::v_bytes(h)) : G::k_bytes(h, G::NK8) + G::v_bytes(h);
+  };
+  while (hp > 1 && need(hp) > budget) hp = (hp + 1) / 2;
+  const size_t smem = need(hp);
+  if (smem > 220 * 1024) return cudaErrorInvalidValue;
+  count_launch();
+  if (th) {
+    static PerDeviceOnce once;
+    if (once.need()) {
+      cudaError_t e = cudaFuncSetAttribute(attn_mma_th_kernel<DK, DV, NKT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+      if (e != cudaSuccess) return e;
+    }
+    return launch_pdl(attn_mma_th_kernel<DK, DV, NKT>, dim3(a.nseq), dim3(kMmaThreads), smem, s, a, hp);
+  }
+  static PerDeviceOnce once;
+  if (once.need()) {
+    cudaError_t e = cudaFuncSetAttribute(attn_mma_kernel<DK, DV, NKT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e != cudaSuccess) return e;
+  }
+  return launch_pdl(attn_mma_kernel<DK, DV, NKT>, dim3(a.nseq), dim3(kMmaThreads), smem, s, a, hp);
+}
+
+}  // namespace
+
+// Returns cudaErrorNotSupported for shapes this kernel is not instantiated for (the caller falls back to attn.cu).
+cudaError_t launch_attention_mma(const AttnArgs& a, cudaStream_t s) {
+  if (a.nseq <= 0) return cudaSuccess;
+  const bool th = a.th1_w != nullptr;
+  if (a.heads > 16 || a.nq > 64 || (a.q_pitch | a.k_pitch | a.v_pitch | a.q_off | a.k_off | a.v_off) % 8) return cudaErrorNotSupported;
+  const int nkt = (a.nk + 7) / 8;
+#define MMA_CASE(DK_, DV_, NKT_, TH_) \
+  if (a.dk == DK_ && a.dv == DV_ && nkt == NKT_ && th == TH_) return mma_launch<DK_, DV_, NKT_>(a, th, s)
+  MMA_CASE(32, 32, 7, false);    // FasterViT-0 window (53 tokens) and level-3 (49 tokens) attention
+  MMA_CASE(32, 32, 2, false);    // FasterViT-0 carrier-token attention (16 tokens)
+  MMA_CASE(48, 48, 7, false);    // FasterViT-2
+  MMA_CASE(48, 48, 2, false);
+  MMA_CASE(32, 128, 7, true);    // EfficientFormerV2 Attention2d (49 tokens, talking heads)
+  MMA_CASE(16, 64, 25, false);   // EfficientFormerV2 Attention2dDownsample (49 queries x 196 keys)
+#undef MMA_CASE
+  return cudaErrorNotSupported;
+}
+
+}  // namespace b200df

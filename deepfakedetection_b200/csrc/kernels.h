@@ -221,6 +221,8 @@ struct AttnArgs {
   void* out;                                     // [nseq*nq, heads*dv]
 };
 cudaError_t launch_attention(const AttnArgs& a, int dtype, cudaStream_t s);
+// bf16, warp-level tensor-core MMA (attn_mma.cu); cudaErrorNotSupported for shapes it is not instantiated for
+cudaError_t launch_attention_mma(const AttnArgs& a, cudaStream_t s);
 
 // ---- transformer glue (vit_ops.cu) ----------------------------------------------------------------------------------
 cudaError_t launch_layernorm(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c,

@@ -17,67 +17,97 @@
 namespace b200df {
 
 // ---- LayerNorm over the innermost dim ------------------------------------------------------------------------
-// One warp per row; the row (C <= 1024) stays in registers between the mean, variance and normalise passes.
-template <typename T>
+// One warp per R rows; the rows (C = 8 * 32 * NV channels at most) stay in registers between the mean, variance and
+// normalise passes, and all R * NV 16-byte loads of a warp are issued before the first reduction (HBM-bound op: what
+// matters is bytes in flight per SM).
+template <typename T, int NV, int R>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const T* __restrict__ x, T* __restrict__ y, const float* __restrict__ gamma,
                  const float* __restrict__ beta, long long rows, int C, float eps) {
   const int lane = threadIdx.x & 31;
-  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long row0 = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * R;
   griddep_wait();
   griddep_launch_dependents();
-  if (row >= rows) return;
+  if (row0 >= rows) return;
   const int nv = C >> 3;
-  float v[4][8];
-  float sum = 0.f;
+  float v[R][NV][8];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int r = 0; r < R; ++r)
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vi = lane + 32 * i;
+      if (row0 + r < rows && vi < nv) {
+        load8<T>(x + (row0 + r) * C + vi * 8, v[r][i]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[r][i][e] = 0.f;
+      }
+    }
+  float g[NV][8], b[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
     const int vi = lane + 32 * i;
     if (vi < nv) {
-      load8<T>(x + row * C + vi * 8, v[i]);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) sum += v[i][e];
+      load8<float>(gamma + vi * 8, g[i]);
+      load8<float>(beta + vi * 8, b[i]);
     }
   }
-  const float mean = warp_sum(sum) / (float)C;
-  float sq = 0.f;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int vi = lane + 32 * i;
-    if (vi < nv) {
+  for (int r = 0; r < R; ++r) {
+    if (row0 + r >= rows) break;
+    float sum = 0.f;
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float d = v[i][e] - mean;
-        sq = fmaf(d, d, sq);
+    for (int i = 0; i < NV; ++i)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) sum += v[r][i][e];   // lanes past the row hold zeros
+    const float mean = warp_sum(sum) / (float)C;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      if (lane + 32 * i < nv) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float d = v[r][i][e] - mean;
+          sq = fmaf(d, d, sq);
+        }
+      }
+    }
+    const float rstd = 1.0f / sqrtf(warp_sum(sq) / (float)C + eps);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vi = lane + 32 * i;
+      if (vi < nv) {
+        float o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = fmaf((v[r][i][e] - mean) * rstd, g[i][e], b[i][e]);
+        store8<T>(y + (row0 + r) * C + vi * 8, o);
       }
     }
   }
-  const float rstd = 1.0f / sqrtf(warp_sum(sq) / (float)C + eps);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int vi = lane + 32 * i;
-    if (vi < nv) {
-      float g[8], b[8], o[8];
-      load8<float>(gamma + vi * 8, g);
-      load8<float>(beta + vi * 8, b);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) o[e] = fmaf((v[i][e] - mean) * rstd, g[e], b[e]);
-      store8<T>(y + row * C + vi * 8, o);
-    }
-  }
+}
+
+template <typename T, int NV, int R>
+static cudaError_t ln_launch(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c, float eps,
+                             cudaStream_t s) {
+  const long long warps = (rows + R - 1) / R;
+  const unsigned grid = (unsigned)((warps + 7) / 8);
+  return launch_pdl(layernorm_kernel<T, NV, R>, dim3(grid), dim3(256), 0, s, reinterpret_cast<const T*>(x),
+                    reinterpret_cast<T*>(y), gamma, beta, rows, c, eps);
 }
 
 cudaError_t launch_layernorm(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c,
                              float eps, int dtype, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
   if (c % 8 || c > 1024) return cudaErrorInvalidValue;
-  const unsigned grid = (unsigned)((rows + 7) / 8);
+  const int nvl = (c / 8 + 31) / 32;   // 16-byte vectors per lane
   count_launch();
-  if (dtype == kBF16)
-    return launch_pdl(layernorm_kernel<bf16>, dim3(grid), dim3(256), 0, s, reinterpret_cast<const bf16*>(x),
-                      reinterpret_cast<bf16*>(y), gamma, beta, rows, c, eps);
-  return launch_pdl(layernorm_kernel<float>, dim3(grid), dim3(256), 0, s, reinterpret_cast<const float*>(x),
-                    reinterpret_cast<float*>(y), gamma, beta, rows, c, eps);
+#define LN_CASE(T_)                                                                         \
+  if (nvl == 1) return ln_launch<T_, 1, 4>(x, y, gamma, beta, rows, c, eps, s);             \
+  if (nvl == 2) return ln_launch<T_, 2, 2>(x, y, gamma, beta, rows, c, eps, s);             \
+  return ln_launch<T_, 4, 1>(x, y, gamma, beta, rows, c, eps, s)
+  if (dtype == kBF16) { LN_CASE(bf16); }
+  LN_CASE(float);
+#undef LN_CASE
 }
 
 // ---- bilinear x2 upsample (align_corners = False) + activation -------------------------------------------------
