@@ -169,10 +169,17 @@ _CLASS_KERNEL = {"dw": "dwconv", "expand": "pwconv_tc_kernel<0, 1, 0>", "project
 def ncu_traffic_per_launch(cls: str):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes) of a kernel class, averaged over its
     launches in the newest committed `ncu --set full` capture of one step (profiles/*_step_metrics.txt)."""
-    files = sorted((ROOT / "profiles").glob("*_step_metrics.txt"))
+    files = sorted((ROOT / "profiles").glob("*_step_metrics.txt"), key=lambda f: f.name)
+    files = [f for f in files if not f.name.endswith(("_b3.txt", "_efv2.txt", "_fv0.txt"))]   # B0 captures only
     key = _CLASS_KERNEL.get(cls)
     if not files or key is None:
         return None, None
+    # the capture must describe the kernels that are being timed: its header carries the source hash it profiled
+    # (tools/ncu_step.py writes `# kernels-sha: <sha16 of csrc>`); a capture of other sources is not reported
+    head = files[-1].read_text().splitlines()[:3]
+    stamp = next((ln.split(":", 1)[1].strip() for ln in head if ln.startswith("# kernels-sha:")), None)
+    if stamp != kernels_sha():
+        return None, f"{files[-1].name} is stale (kernels-sha {stamp} != {kernels_sha()})"
     tot, cnt = 0.0, 0
     for line in files[-1].read_text().splitlines():
         if line.startswith("#") or key not in line:
@@ -184,6 +191,18 @@ def ncu_traffic_per_launch(cls: str):
             tot += float(nums[1]) + float(nums[2])
             cnt += 1
     return (tot / cnt * 1e6, files[-1].name) if cnt else (None, None)
+
+
+def kernels_sha() -> str:
+    """sha16 over the CUDA sources: identifies the build an ncu capture belongs to."""
+    import hashlib
+
+    h = hashlib.sha256()
+    for f in sorted((ROOT / "deepfakedetection_b200" / "csrc").glob("*")):
+        if f.suffix in (".cu", ".cuh", ".h", ".inc"):
+            h.update(f.name.encode())
+            h.update(f.read_bytes())
+    return h.hexdigest()[:16]
 
 
 def peaks() -> tuple[dict, str]:

@@ -10,8 +10,9 @@
 // back between the two products.  With register-resident fragments the whole (head, 16-query block) unit is one warp's
 // work, flash-attention style: the S accumulators of two adjacent 8-key tiles ARE the A fragment of the P.V product, the
 // softmax is two quad shuffles per row, and nothing but q, k, v is read and nothing but `out` is written.
-//   * staging (per pass of `hp` heads): K rows as they are ([key][d], pitch d+8 -> conflict-free 32-bit B-fragment loads),
-//     V TRANSPOSED ([d][key], pitch keys+8) so that the P.V B fragment is a 32-bit load too; pads are zeroed;
+//   * staging (per pass of `hp` heads): K and V rows as they are ([key][d], pitch d+8, 16-byte copies): the q.k^T B
+//     fragment is a conflict-free 32-bit load, the P.V B fragment (keys x d, i.e. V transposed) comes out of
+//     `ldmatrix.trans`, so no transposition is ever written; key pads are zeroed;
 //   * Q fragments come straight from global memory (L2-hot GEMM output), the bias table from L2;
 //   * talking heads (EfficientFormerV2) couple the heads between the two products: S of all heads goes to shared memory in
 //     fp32, the two 8x8 mixes and the softmax run there (as in attn.cu), and the P.V A fragments are built from it.
@@ -39,10 +40,10 @@ struct AttnGeom {
   static constexpr int NK8 = NKT * 8;                 // keys padded to whole 8-key S tiles
   static constexpr int NKP = (NK8 + 15) / 16 * 16;    // keys padded to whole 16-key P.V steps
   static constexpr int KP = DK + 8;                   // K row pitch (bf16 elements)
-  static constexpr int VP = NKP + 8;                  // V^T row pitch
+  static constexpr int VP = DV + 8;                   // V row pitch (bf16 elements; 16-byte aligned rows for ldmatrix)
   static constexpr int SP = NKP + 8;                  // fp32 score row pitch (talking-head path)
   static constexpr size_t k_bytes(int heads, int nk) { return (size_t)heads * ((nk + 7) / 8 * 8) * KP * 2; }
-  static constexpr size_t v_bytes(int heads) { return (size_t)heads * DV * VP * 2; }
+  static constexpr size_t v_bytes(int heads) { return (size_t)heads * NKP * VP * 2; }
 };
 
 // ---- staging ---------------------------------------------------------------------------------------------------
@@ -63,7 +64,7 @@ __device__ __forceinline__ void stage_k(const AttnArgs& a, int seq, int h0, int 
 }
 
 template <int DK, int DV, int NKT>
-__device__ __forceinline__ void stage_vt(const AttnArgs& a, int seq, int h0, int nh, bf16* Vt) {
+__device__ __forceinline__ void stage_vt(const AttnArgs& a, int seq, int h0, int nh, bf16* Vs) {
   using G = AttnGeom<DK, DV, NKT>;
   const bf16* v = reinterpret_cast<const bf16*>(a.v);
   for (int idx = threadIdx.x; idx < nh * G::NKP * (DV / 8); idx += kMmaThreads) {
@@ -73,14 +74,15 @@ __device__ __forceinline__ void stage_vt(const AttnArgs& a, int seq, int h0, int
     uint4 raw = make_uint4(0u, 0u, 0u, 0u);
     if (j < a.nk)
       raw = __ldg(reinterpret_cast<const uint4*>(v + ((size_t)seq * a.nk + j) * a.v_pitch + a.v_off + (h0 + hl) * DV + c8 * 8));
-    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
-    bf16* dst = Vt + ((size_t)hl * DV + c8 * 8) * G::VP + j;
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      reinterpret_cast<uint16_t*>(dst)[(2 * e) * G::VP] = (uint16_t)(w[e] & 0xffffu);
-      reinterpret_cast<uint16_t*>(dst)[(2 * e + 1) * G::VP] = (uint16_t)(w[e] >> 16);
-    }
+    *reinterpret_cast<uint4*>(Vs + ((size_t)hl * G::NKP + j) * G::VP + c8 * 8) = raw;
   }
+}
+
+// B fragment of the P.V product for keys [k0, k0 + 16) x channels [d0, d0 + 8): V is staged [key][d], the fragment wants
+// (key pair, channel) per thread = the transposed 8x8 tiles -> ldmatrix.trans (lanes 0-15 supply the 16 key-row addresses)
+__device__ __forceinline__ void ldmatrix_x2_trans(uint32_t& b0, uint32_t& b1, const bf16* row_ptr) {
+  const uint32_t addr = static_cast<uint32_t>(__cvta_generic_to_shared(row_ptr));
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0, %1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(addr));
 }
 
 // ---- S = q k^T for one (head, 16-query block): s[NKT][4] in the mma C layout -------------------------------------------
@@ -128,8 +130,9 @@ __device__ __forceinline__ void pv_unit(const AttnArgs& a, int seq, int h, int r
     afrag(kt, af);
 #pragma unroll
     for (int dt = 0; dt < DV / 8; ++dt) {
-      const bf16* vr = Vh + (size_t)(dt * 8 + g) * G::VP + kt * 16 + 2 * t;
-      mma_bf16_16816(o[dt], af, *reinterpret_cast<const uint32_t*>(vr), *reinterpret_cast<const uint32_t*>(vr + 8));
+      uint32_t b0, b1;
+      ldmatrix_x2_trans(b0, b1, Vh + (size_t)(kt * 16 + (lane & 15)) * G::VP + dt * 8);
+      mma_bf16_16816(o[dt], af, b0, b1);
     }
   }
   const int oc = a.heads * DV;
@@ -223,7 +226,7 @@ attn_mma_kernel(const AttnArgs a, int hp) {
           af[3] = 0u;
         }
       };
-      pv_unit<DK, DV, NKT>(a, seq, h, r0, Vt + (size_t)hl * DV * G::VP, afrag, 1.0f / sum[0], 1.0f / sum[1]);
+      pv_unit<DK, DV, NKT>(a, seq, h, r0, Vt + (size_t)hl * G::NKP * G::VP, afrag, 1.0f / sum[0], 1.0f / sum[1]);
     }
   }
 }
@@ -322,7 +325,7 @@ attn_mma_th_kernel(const AttnArgs a, int hp) {
         af[2] = ok0 ? pack_bf16x2(p01.x, p01.y) : 0u;
         af[3] = ok1 ? pack_bf16x2(p11.x, p11.y) : 0u;
       };
-      pv_unit<DK, DV, NKT>(a, seq, h, r0, Vt + (size_t)hl * DV * G::VP, afrag, 1.0f, 1.0f);
+      pv_unit<DK, DV, NKT>(a, seq, h, r0, Vt + (size_t)hl * G::NKP * G::VP, afrag, 1.0f, 1.0f);
     }
   }
 }
@@ -330,7 +333,7 @@ attn_mma_th_kernel(const AttnArgs a, int hp) {
 template <int DK, int DV, int NKT>
 cudaError_t mma_launch(const AttnArgs& a, bool th, cudaStream_t s) {
   using G = AttnGeom<DK, DV, NKT>;
-  const size_t budget = th ? 200 * 1024 : 72 * 1024;   // no talking heads: three CTAs per SM
+  const size_t budget = th ? 200 * 1024 : 100 * 1024;  // no talking heads: two CTAs per SM
   const size_t s_bytes = th ? (((size_t)a.heads * a.nq * G::SP * sizeof(float) + 15) & ~size_t(15)) : 0;
   int hp = a.heads;
   auto need = [&](int h) {

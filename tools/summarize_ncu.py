@@ -16,6 +16,20 @@ def short(name: str) -> str:
     return (m.group(1) + (m.group(2) or "")) if m else name[:40]
 
 
+def stamp() -> None:
+    """Which build the capture belongs to (bench.py refuses traffic numbers from a capture of other kernel sources)."""
+    import subprocess
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    sys.path.insert(0, str(root))
+    from bench import kernels_sha
+
+    commit = subprocess.run(["git", "-C", str(root), "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+    print(f"# kernels-sha: {kernels_sha()}")
+    print(f"# summarised at commit {commit} (capture taken on the tree with that kernels-sha)")
+
+
 def launches(path: str) -> None:
     rows = [r for r in csv.reader(open(path, errors="ignore")) if len(r) > 10]
     hdr = rows[0]
@@ -40,6 +54,7 @@ def step(path: str) -> None:
     rows = list(csv.reader(open(path, errors="ignore")))
     hdr, data = rows[0], rows[2:]
     idx = {h: i for i, h in enumerate(hdr)}
+    stamp()
     cols = [("gpu__time_duration.sum", "us", 8), ("dram__bytes_read.sum", "rdMB", 8), ("dram__bytes_write.sum", "wrMB", 8),
             ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram%", 6),
             ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm%", 6),
@@ -93,6 +108,7 @@ def details(path: str) -> None:
                 except ValueError:
                     pass
             d[nm] = val
+    stamp()
     print("# one forward step (N=256, bf16), ncu --set full --clock-control none (details page, one line per launch)")
     print(f"{'#':>3s} {'kernel':44s} " + " ".join(f"{c[1]:>{c[2]}s}" for c in want))
     tot = 0.0
