@@ -234,11 +234,21 @@ def roc_auc_device(targets: torch.Tensor, scores: torch.Tensor) -> float:
 
 def compute_metrics_device(records: torch.Tensor, num_classes: int, threshold: float | None = None) -> dict[str, Any]:
     """`compute_metrics` (orchestrator.py:605-635) on the gathered device records [n, C+2] without the O(N)
-    host work: only the confusion matrix / AUC counts cross PCIe."""
+    host work: only the confusion matrix / AUC counts cross PCIe.
+
+    Device scope = the reference's deployed case: binary heads with both classes present.  Everything else -- more than
+    two classes (sklearn's one-vs-rest AUC, :624-626) or data in which a class never occurs (sklearn then returns a
+    confusion matrix over the OBSERVED labels only) -- is handed to `compute_metrics` on the host, so the numbers are the
+    reference's in every case."""
     c = records.shape[1] - 2
     probs = records[:, :c]
     preds = records[:, c].round().long()
     targets = records[:, c + 1].round().long()
+    seen = torch.unique(torch.cat([targets, preds if not (num_classes == 2 and threshold is not None) else
+                                   (probs[:, 1] >= threshold).long()]))
+    if records.shape[0] == 0 or num_classes != 2 or seen.numel() < num_classes or int(targets.min()) < 0 or int(targets.max()) >= num_classes:
+        p, q, t = unpack_records(records)
+        return compute_metrics(p, q, t, num_classes, threshold)
     if num_classes == 2 and threshold is not None:
         preds = (probs[:, 1] >= threshold).long()   # the reference's own expression (orchestrator.py:609)
     cm = confusion_matrix_device(targets, preds, num_classes)

@@ -207,3 +207,39 @@ def test_out_of_range_cam_class_is_rejected(name):
             model.forward_cam(x, torch.tensor(bad))
         assert ei.value.code == _lib.E_INVALID
     model.forward_cam(x, torch.tensor([0, 1]))   # in range: fine
+
+
+# ---- metrics tail outside the binary / both-classes-present case ---------------------------------------------
+@pytest.mark.parametrize("case", ["multiclass", "single_class"])
+def test_device_metrics_tail_matches_reference_expressions_outside_binary(case):
+    from deepfakedetection_b200 import evaluate
+
+    g = torch.Generator().manual_seed(4)
+    if case == "multiclass":
+        c, n = 4, 500
+        logits = torch.randn(n, c, generator=g) * 2
+        targets = torch.randint(0, c, (n,), generator=g)
+    else:
+        c, n = 2, 64
+        logits = torch.randn(n, c, generator=g)
+        targets = torch.zeros(n, dtype=torch.long)
+    probs = torch.softmax(logits, 1)
+    rec = torch.cat([probs, probs.argmax(1, keepdim=True).float(), targets.view(-1, 1).float()], 1).cuda()
+    got = evaluate.compute_metrics_device(rec, c, threshold=0.5 if c == 2 else None)
+    want = evaluate.compute_metrics(probs, probs.argmax(1), targets, c, threshold=0.5 if c == 2 else None)
+    assert got["confusion_matrix"] == want["confusion_matrix"]
+    assert abs(got["accuracy"] - want["accuracy"]) < 1e-6
+    assert ("roc_auc" in got) == ("roc_auc" in want)
+    if "roc_auc" in want:
+        assert abs(got["roc_auc"] - want["roc_auc"]) < 1e-9
+
+
+# ---- uint8 path input validation ---------------------------------------------------------------------------------
+def test_forward_u8_rejects_wrong_layouts(oracle_model):
+    model = build(oracle_model, "efficientnet_b0")
+    with pytest.raises(ValueError, match="uint8"):
+        model.forward_u8(torch.zeros(2, 3, 224, 224, dtype=torch.uint8, device="cuda"))       # CHW instead of HWC
+    with pytest.raises(ValueError, match="uint8"):
+        model.forward_u8(torch.zeros(2, 160, 160, 3, dtype=torch.uint8, device="cuda"))       # wrong crop size
+    with pytest.raises(ValueError, match="3 entries"):
+        model.forward_u8(torch.zeros(2, 224, 224, 3, dtype=torch.uint8, device="cuda"), mean=(0.5,), std=(0.5,))
