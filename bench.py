@@ -194,14 +194,15 @@ def ncu_traffic_per_launch(cls: str):
 
 
 def kernels_sha() -> str:
-    """sha16 over the CUDA sources: identifies the build an ncu capture belongs to."""
+    """sha16 over the device sources of the EfficientNet path: identifies the kernels an ncu capture belongs to."""
     import hashlib
 
     h = hashlib.sha256()
-    for f in sorted((ROOT / "deepfakedetection_b200" / "csrc").glob("*")):
-        if f.suffix in (".cu", ".cuh", ".h", ".inc"):
-            h.update(f.name.encode())
-            h.update(f.read_bytes())
+    for name in ("act.h", "common.cuh", "tc.cuh", "stem.cu", "stem_tc.cu", "dwconv.cu", "dwconv_tma.cu", "se.cu", "pwconv_simt.cu",
+                 "pwconv_tc.cu", "tail.cu"):
+        f = ROOT / "deepfakedetection_b200" / "csrc" / name
+        h.update(name.encode())
+        h.update(f.read_bytes())
     return h.hexdigest()[:16]
 
 

@@ -52,7 +52,9 @@ def launches(path: str) -> None:
 
 def step(path: str) -> None:
     rows = list(csv.reader(open(path, errors="ignore")))
-    hdr, data = rows[0], rows[2:]
+    h0 = next(i for i, r in enumerate(rows) if r and r[0] == "ID")   # ncu's own messages may precede the table
+    hdr, units, data = rows[h0], rows[h0 + 1], rows[h0 + 2:]
+    hdr = [h.split(".TriageCompute.")[-1] if ".TriageCompute." in h else h for h in hdr]
     idx = {h: i for i, h in enumerate(hdr)}
     stamp()
     cols = [("gpu__time_duration.sum", "us", 8), ("dram__bytes_read.sum", "rdMB", 8), ("dram__bytes_write.sum", "wrMB", 8),
@@ -74,10 +76,16 @@ def step(path: str) -> None:
         if len(r) < len(hdr):
             continue
         vals = []
-        for key, _, w in cols:
+        for key, label, w in cols:
             v = r[idx[key]] if key in idx else "-"
             try:
-                v = f"{float(v):.1f}" if "." in v else v
+                if label in ("us", "rdMB", "wrMB"):   # normalise whatever unit this ncu version chose
+                    u = units[idx[key]].lower()
+                    scale = {"ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "byte": 1e-6,
+                             "kbyte": 1e-3, "mbyte": 1.0, "gbyte": 1e3}.get(u, 1.0)
+                    v = f"{float(v.replace(',', '')) * scale:.1f}"
+                else:
+                    v = f"{float(v):.1f}" if "." in v else v
             except ValueError:
                 pass
             vals.append(f"{v:>{w}s}")
