@@ -53,9 +53,12 @@ __device__ __forceinline__ void stage_k(const AttnArgs& a, int seq, int h0, int 
   const bf16* k = reinterpret_cast<const bf16*>(a.k);
   const int rows = G::NK8;
   for (int idx = threadIdx.x; idx < nh * rows * (DK / 8); idx += kMmaThreads) {
-    const int c8 = idx % (DK / 8);
-    const int r = idx / (DK / 8);
-    const int j = r % rows, hl = r / rows;
+    // 8 consecutive lanes take 8 consecutive rows of ONE 16-byte column: with the 16-byte-odd row pitch the 128-bit
+    // shared stores of a quarter warp land in 8 different bank groups (row-major lane order measured 8-way conflicts)
+    int r = idx >> 3;
+    const int c8 = r % (DK / 8);
+    r /= (DK / 8);
+    const int j = (r % (rows / 8)) * 8 + (idx & 7), hl = r / (rows / 8);
     uint4 v = make_uint4(0u, 0u, 0u, 0u);
     if (j < a.nk)
       v = __ldg(reinterpret_cast<const uint4*>(k + ((size_t)seq * a.nk + j) * a.k_pitch + a.k_off + (h0 + hl) * DK + c8 * 8));
@@ -68,9 +71,10 @@ __device__ __forceinline__ void stage_vt(const AttnArgs& a, int seq, int h0, int
   using G = AttnGeom<DK, DV, NKT>;
   const bf16* v = reinterpret_cast<const bf16*>(a.v);
   for (int idx = threadIdx.x; idx < nh * G::NKP * (DV / 8); idx += kMmaThreads) {
-    const int c8 = idx % (DV / 8);
-    const int r = idx / (DV / 8);
-    const int j = r % G::NKP, hl = r / G::NKP;
+    int r = idx >> 3;
+    const int c8 = r % (DV / 8);
+    r /= (DV / 8);
+    const int j = (r % (G::NKP / 8)) * 8 + (idx & 7), hl = r / (G::NKP / 8);
     uint4 raw = make_uint4(0u, 0u, 0u, 0u);
     if (j < a.nk)
       raw = __ldg(reinterpret_cast<const uint4*>(v + ((size_t)seq * a.nk + j) * a.v_pitch + a.v_off + (h0 + hl) * DV + c8 * 8));
@@ -183,19 +187,37 @@ attn_mma_kernel(const AttnArgs a, int hp) {
       qk_unit<DK, DV, NKT>(a, seq, h, r0, Ks + (size_t)hl * G::NK8 * G::KP, s);
       // scale + bias, key mask, row max / sum (two rows per thread: g and g + 8; a row lives in one quad)
       float mx[2] = {-INFINITY, -INFINITY};
+      if (a.bias_frag) {
+        // bias in the accumulator-fragment order (one float4 per thread and key tile; masked keys hold -inf, rows past
+        // the sequence 0): NKT independent 16-byte loads instead of 4*NKT predicated scalar ones
+        const float4* bf = reinterpret_cast<const float4*>(a.bias_frag) + ((size_t)(h * RB + r0 / 16) * NKT) * 32 + lane;
+        float4 b4[NKT];
 #pragma unroll
-      for (int jt = 0; jt < NKT; ++jt)
+        for (int jt = 0; jt < NKT; ++jt) b4[jt] = __ldg(bf + jt * 32);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int i = r0 + g + 8 * (e >> 1), j = jt * 8 + 2 * t + (e & 1);
-          float v = -INFINITY;
-          if (j < a.nk) {
-            v = s[jt][e] * a.scale;
-            if (a.bias && i < a.nq) v += __ldg(a.bias + ((size_t)h * a.nq + i) * a.nk + j);
-          }
-          s[jt][e] = v;
-          mx[e >> 1] = fmaxf(mx[e >> 1], v);
+        for (int jt = 0; jt < NKT; ++jt) {
+          s[jt][0] = fmaf(s[jt][0], a.scale, b4[jt].x);
+          s[jt][1] = fmaf(s[jt][1], a.scale, b4[jt].y);
+          s[jt][2] = fmaf(s[jt][2], a.scale, b4[jt].z);
+          s[jt][3] = fmaf(s[jt][3], a.scale, b4[jt].w);
+          mx[0] = fmaxf(mx[0], fmaxf(s[jt][0], s[jt][1]));
+          mx[1] = fmaxf(mx[1], fmaxf(s[jt][2], s[jt][3]));
         }
+      } else {
+#pragma unroll
+        for (int jt = 0; jt < NKT; ++jt)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int i = r0 + g + 8 * (e >> 1), j = jt * 8 + 2 * t + (e & 1);
+            float v = -INFINITY;
+            if (j < a.nk) {
+              v = s[jt][e] * a.scale;
+              if (a.bias && i < a.nq) v += __ldg(a.bias + ((size_t)h * a.nq + i) * a.nk + j);
+            }
+            s[jt][e] = v;
+            mx[e >> 1] = fmaxf(mx[e >> 1], v);
+          }
+      }
       float sum[2] = {0.f, 0.f};
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
@@ -244,6 +266,13 @@ attn_mma_th_kernel(const AttnArgs a, int hp) {
   bf16* Vt = reinterpret_cast<bf16*>(region);                                      // hp heads at a time (output phase)
   const int seq = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int RB = (nq + 15) / 16;
+  __shared__ __align__(16) float thw[2 * (16 * 16 + 16)];
+  for (int i = threadIdx.x; i < 2 * (H * H + H); i += kMmaThreads) {   // weights only: before the dependency wait
+    const int pass = i / (H * H + H), r = i - pass * (H * H + H);
+    const float* w = pass == 0 ? a.th1_w : a.th2_w;
+    const float* b = pass == 0 ? a.th1_b : a.th2_b;
+    thw[pass * (16 * 16 + 16) + (r < H * H ? r : 16 * 16 + r - H * H)] = r < H * H ? __ldg(w + r) : __ldg(b + r - H * H);
+  }
   griddep_wait();
   griddep_launch_dependents();
   // ---- scores ----
@@ -253,17 +282,24 @@ attn_mma_th_kernel(const AttnArgs a, int hp) {
     const int h = u / RB, r0 = (u - h * RB) * 16;
     float s[NKT][4];
     qk_unit<DK, DV, NKT>(a, seq, h, r0, Ks + (size_t)h * G::NK8 * G::KP, s);
+    const float4* bf = a.bias_frag ? reinterpret_cast<const float4*>(a.bias_frag) + ((size_t)(h * RB + r0 / 16) * NKT) * 32 + lane
+                                   : nullptr;
+    float4 b4[NKT];
 #pragma unroll
-    for (int jt = 0; jt < NKT; ++jt)
+    for (int jt = 0; jt < NKT; ++jt) b4[jt] = bf ? __ldg(bf + jt * 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int jt = 0; jt < NKT; ++jt) {
+      const float bb[4] = {b4[jt].x, b4[jt].y, b4[jt].z, b4[jt].w};
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const int i = r0 + g + 8 * (e >> 1), j = jt * 8 + 2 * t + (e & 1);
         if (i < nq && j < nk) {
-          float v = s[jt][e] * a.scale;
-          if (a.bias) v += __ldg(a.bias + ((size_t)h * nq + i) * nk + j);
+          float v = fmaf(s[jt][e], a.scale, bb[e]);
+          if (!bf && a.bias) v += __ldg(a.bias + ((size_t)h * nq + i) * nk + j);
           S[((size_t)h * nq + i) * G::SP + j] = v;
         }
       }
+    }
   }
   // zero the key padding of every row once: it is read as P = 0 by the 16-key steps of the second product
   for (int idx = threadIdx.x; idx < H * nq * (G::SP - nk); idx += kMmaThreads) {
@@ -273,16 +309,31 @@ attn_mma_th_kernel(const AttnArgs a, int hp) {
   __syncthreads();
   // ---- talking head 1, softmax over keys, talking head 2 (as attn.cu) ----
   for (int pass = 0; pass < 2; ++pass) {
-    const float* w = pass == 0 ? a.th1_w : a.th2_w;
-    const float* b = pass == 0 ? a.th1_b : a.th2_b;
+    const float* w = thw + pass * (16 * 16 + 16);   // [H][H] mix + [H] bias, staged in shared memory at kernel start
+    const float* b = w + 16 * 16;
     for (int idx = threadIdx.x; idx < nq * nk; idx += kMmaThreads) {
       const int i = idx / nk, j = idx - i * nk;
-      float v[16];
-      for (int h = 0; h < H; ++h) v[h] = S[((size_t)h * nq + i) * G::SP + j];
-      for (int ho = 0; ho < H; ++ho) {
-        float o = __ldg(b + ho);
-        for (int h = 0; h < H; ++h) o = fmaf(__ldg(w + ho * H + h), v[h], o);
-        S[((size_t)ho * nq + i) * G::SP + j] = o;
+      float* sp = S + (size_t)i * G::SP + j;
+      const size_t hs = (size_t)nq * G::SP;
+      if (H == 8) {
+        float v[8], o[8];
+#pragma unroll
+        for (int h = 0; h < 8; ++h) v[h] = sp[h * hs];
+#pragma unroll
+        for (int ho = 0; ho < 8; ++ho) {
+          const float4 w0 = *reinterpret_cast<const float4*>(w + ho * 8), w1 = *reinterpret_cast<const float4*>(w + ho * 8 + 4);
+          o[ho] = b[ho] + w0.x * v[0] + w0.y * v[1] + w0.z * v[2] + w0.w * v[3] + w1.x * v[4] + w1.y * v[5] + w1.z * v[6] + w1.w * v[7];
+        }
+#pragma unroll
+        for (int h = 0; h < 8; ++h) sp[h * hs] = o[h];
+      } else {
+        float v[16];
+        for (int h = 0; h < H; ++h) v[h] = sp[h * hs];
+        for (int ho = 0; ho < H; ++ho) {
+          float o = b[ho];
+          for (int h = 0; h < H; ++h) o = fmaf(w[ho * H + h], v[h], o);
+          sp[ho * hs] = o;
+        }
       }
     }
     __syncthreads();
@@ -360,6 +411,47 @@ cudaError_t mma_launch(const AttnArgs& a, bool th, cudaStream_t s) {
 }
 
 }  // namespace
+
+// ---- bias table in accumulator-fragment order ---------------------------------------------------------------------------
+// element (h, rb, jt, lane, e): query i = rb*16 + (lane>>2) + 8*(e>>1), key j = jt*8 + 2*(lane&3) + (e&1);
+// value = bias[h][i][j], 0 for i >= nq, -inf for j >= nk (the key mask comes for free with the bias add).
+size_t attention_bias_frag_elems(int heads, int nq, int nk) {
+  return (size_t)heads * ((nq + 15) / 16) * ((nk + 7) / 8) * 32 * 4;
+}
+
+void attention_bias_frag_host(const float* bias, int heads, int nq, int nk, float* out) {
+  const int RB = (nq + 15) / 16, NKT = (nk + 7) / 8;
+  for (int h = 0; h < heads; ++h)
+    for (int rb = 0; rb < RB; ++rb)
+      for (int jt = 0; jt < NKT; ++jt)
+        for (int lane = 0; lane < 32; ++lane)
+          for (int e = 0; e < 4; ++e) {
+            const int i = rb * 16 + (lane >> 2) + 8 * (e >> 1), j = jt * 8 + 2 * (lane & 3) + (e & 1);
+            const float v = j >= nk ? -INFINITY : (i >= nq ? 0.f : (bias ? bias[((size_t)h * nq + i) * nk + j] : 0.f));
+            out[((((size_t)h * RB + rb) * NKT + jt) * 32 + lane) * 4 + e] = v;
+          }
+}
+
+namespace {
+__global__ void bias_frag_kernel(const float* __restrict__ bias, int heads, int nq, int nk, float* __restrict__ out, size_t total) {
+  const int RB = (nq + 15) / 16, NKT = (nk + 7) / 8;
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const int e = (int)(idx & 3), lane = (int)((idx >> 2) & 31);
+    size_t r = idx >> 7;
+    const int jt = (int)(r % NKT);
+    r /= NKT;
+    const int rb = (int)(r % RB), h = (int)(r / RB);
+    const int i = rb * 16 + (lane >> 2) + 8 * (e >> 1), j = jt * 8 + 2 * (lane & 3) + (e & 1);
+    out[idx] = j >= nk ? -INFINITY : (i >= nq ? 0.f : (bias ? bias[((size_t)h * nq + i) * nk + j] : 0.f));
+  }
+}
+}  // namespace
+
+cudaError_t launch_attention_bias_frag(const float* bias, int heads, int nq, int nk, float* out, cudaStream_t s) {
+  const size_t total = attention_bias_frag_elems(heads, nq, nk);
+  bias_frag_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(bias, heads, nq, nk, out, total);
+  return cudaGetLastError();
+}
 
 // Returns cudaErrorNotSupported for shapes this kernel is not instantiated for (the caller falls back to attn.cu).
 cudaError_t launch_attention_mma(const AttnArgs& a, cudaStream_t s) {

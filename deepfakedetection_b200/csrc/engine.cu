@@ -1265,7 +1265,18 @@ extern "C" int b200df_k_attention(const void* q, const void* k, const void* v, i
   a.nseq = nseq; a.nq = nq; a.nk = nk; a.dk = dk; a.dv = dv; a.heads = heads; a.scale = scale;
   a.bias = bias; a.th1_w = th1_w; a.th1_b = th1_b; a.th2_w = th2_w; a.th2_b = th2_b;
   a.vlocal = vlocal; a.act = act; a.out = out;
-  CU_OK(launch_attention(a, dtype, S(stream)));
+  float* frag = nullptr;
+  if (dtype == kBF16 && bias) {   // test-only convenience: the engine lays the table out once at finalize
+    CU_OK(cudaMalloc(&frag, attention_bias_frag_elems(heads, nq, nk) * sizeof(float)));
+    CU_OK(launch_attention_bias_frag(bias, heads, nq, nk, frag, S(stream)));
+    a.bias_frag = frag;
+  }
+  cudaError_t e = launch_attention(a, dtype, S(stream));
+  if (frag) {
+    cudaStreamSynchronize(S(stream));
+    cudaFree(frag);
+  }
+  CU_OK(e);
   return B200DF_OK;
 }
 

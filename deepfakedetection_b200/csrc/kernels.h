@@ -214,6 +214,7 @@ struct AttnArgs {
   int nseq, nq, nk, dk, dv, heads;
   float scale;
   const float* bias;                             // [heads, nq, nk] fp32 or nullptr
+  const float* bias_frag;                        // the same table in mma accumulator-fragment order (attn_mma.cu), or nullptr
   const float* th1_w; const float* th1_b;        // talking heads: [heads, heads], [heads] (nullptr = none)
   const float* th2_w; const float* th2_b;
   const void* vlocal;                            // [nseq*nq, heads*dv] added to the output, or nullptr
@@ -223,6 +224,9 @@ struct AttnArgs {
 cudaError_t launch_attention(const AttnArgs& a, int dtype, cudaStream_t s);
 // bf16, warp-level tensor-core MMA (attn_mma.cu); cudaErrorNotSupported for shapes it is not instantiated for
 cudaError_t launch_attention_mma(const AttnArgs& a, cudaStream_t s);
+size_t attention_bias_frag_elems(int heads, int nq, int nk);
+void attention_bias_frag_host(const float* bias, int heads, int nq, int nk, float* out);
+cudaError_t launch_attention_bias_frag(const float* bias, int heads, int nq, int nk, float* out, cudaStream_t s);
 
 // ---- transformer glue (vit_ops.cu) ----------------------------------------------------------------------------------
 cudaError_t launch_layernorm(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c,
