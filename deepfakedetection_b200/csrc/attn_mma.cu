@@ -307,52 +307,111 @@ attn_mma_th_kernel(const AttnArgs a, int hp) {
     S[(size_t)r * G::SP + nk + c] = 0.f;
   }
   __syncthreads();
-  // ---- talking head 1, softmax over keys, talking head 2 (as attn.cu) ----
-  for (int pass = 0; pass < 2; ++pass) {
-    const float* w = thw + pass * (16 * 16 + 16);   // [H][H] mix + [H] bias, staged in shared memory at kernel start
-    const float* b = w + 16 * 16;
-    for (int idx = threadIdx.x; idx < nq * nk; idx += kMmaThreads) {
-      const int i = idx / nk, j = idx - i * nk;
-      float* sp = S + (size_t)i * G::SP + j;
-      const size_t hs = (size_t)nq * G::SP;
-      if (H == 8) {
-        float v[8], o[8];
+  // ---- talking head 1 -> softmax over keys -> talking head 2 ----
+  if (NKT == 7 && H == 8) {
+    // EfficientFormerV2's shape: ONE pass over S.  A quarter warp owns a query row for ALL heads (8 lanes x 7 keys each,
+    // 8 heads: 56 values per lane in registers), so the two 8x8 head mixes are register-local and the softmax
+    // reductions are three shuffles inside the 8-lane group; four rows per warp are in flight at once.
+    const float* w1 = thw, *b1 = thw + 256, *w2 = thw + 272, *b2 = thw + 272 + 256;
+    const int q4 = lane >> 3, l8 = lane & 7;
+    const size_t hs = (size_t)nq * G::SP;
+    for (int base = warp * 4; base < nq; base += kMmaWarps * 4) {
+      const int i = base + q4;
+      const bool row_ok = i < nq;
+      float* sp = S + (size_t)min(i, nq - 1) * G::SP + l8;
+      float v[8][7], o[8][7];
 #pragma unroll
-        for (int h = 0; h < 8; ++h) v[h] = sp[h * hs];
+      for (int h = 0; h < 8; ++h)
 #pragma unroll
-        for (int ho = 0; ho < 8; ++ho) {
-          const float4 w0 = *reinterpret_cast<const float4*>(w + ho * 8), w1 = *reinterpret_cast<const float4*>(w + ho * 8 + 4);
-          o[ho] = b[ho] + w0.x * v[0] + w0.y * v[1] + w0.z * v[2] + w0.w * v[3] + w1.x * v[4] + w1.y * v[5] + w1.z * v[6] + w1.w * v[7];
+        for (int k = 0; k < 7; ++k) v[h][k] = sp[h * hs + 8 * k];     // j = l8 + 8k < 56 <= SP: pads hold zeros
+#pragma unroll
+      for (int ho = 0; ho < 8; ++ho) {
+        const float4 wa = *reinterpret_cast<const float4*>(w1 + ho * 8), wb = *reinterpret_cast<const float4*>(w1 + ho * 8 + 4);
+        const float bb = b1[ho];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+          const float x = bb + wa.x * v[0][k] + wa.y * v[1][k] + wa.z * v[2][k] + wa.w * v[3][k] + wb.x * v[4][k] +
+                          wb.y * v[5][k] + wb.z * v[6][k] + wb.w * v[7][k];
+          o[ho][k] = l8 + 8 * k < nk ? x : -INFINITY;
+          mx = fmaxf(mx, o[ho][k]);
         }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+        float sum = 0.f;
 #pragma unroll
-        for (int h = 0; h < 8; ++h) sp[h * hs] = o[h];
-      } else {
-        float v[16];
-        for (int h = 0; h < H; ++h) v[h] = sp[h * hs];
-        for (int ho = 0; ho < H; ++ho) {
-          float o = b[ho];
-          for (int h = 0; h < H; ++h) o = fmaf(w[ho * H + h], v[h], o);
-          sp[ho * hs] = o;
+        for (int k = 0; k < 7; ++k) {
+          o[ho][k] = __expf(o[ho][k] - mx);
+          sum += o[ho][k];
+        }
+        sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+        sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+        sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+        const float inv = 1.0f / sum;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) o[ho][k] *= inv;
+      }
+#pragma unroll
+      for (int ho = 0; ho < 8; ++ho) {
+        const float4 wa = *reinterpret_cast<const float4*>(w2 + ho * 8), wb = *reinterpret_cast<const float4*>(w2 + ho * 8 + 4);
+        const float bb = b2[ho];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+          const float x = bb + wa.x * o[0][k] + wa.y * o[1][k] + wa.z * o[2][k] + wa.w * o[3][k] + wb.x * o[4][k] +
+                          wb.y * o[5][k] + wb.z * o[6][k] + wb.w * o[7][k];
+          if (row_ok && l8 + 8 * k < nk) sp[ho * hs + 8 * k] = x;
         }
       }
     }
     __syncthreads();
-    if (pass == 0) {
-      for (int r = warp; r < H * nq; r += kMmaWarps) {
-        float* row = S + (size_t)r * G::SP;
-        float mx = -INFINITY;
-        for (int j = lane; j < nk; j += 32) mx = fmaxf(mx, row[j]);
-        mx = warp_max(mx);
-        float sum = 0.f;
-        for (int j = lane; j < nk; j += 32) {
-          const float e = __expf(row[j] - mx);
-          row[j] = e;
-          sum += e;
+  } else {
+    for (int pass = 0; pass < 2; ++pass) {
+      const float* w = thw + pass * (16 * 16 + 16);   // [H][H] mix + [H] bias, staged in shared memory at kernel start
+      const float* b = w + 16 * 16;
+      for (int idx = threadIdx.x; idx < nq * nk; idx += kMmaThreads) {
+        const int i = idx / nk, j = idx - i * nk;
+        float* sp = S + (size_t)i * G::SP + j;
+        const size_t hs = (size_t)nq * G::SP;
+        if (H == 8) {
+          float v[8], o[8];
+  #pragma unroll
+          for (int h = 0; h < 8; ++h) v[h] = sp[h * hs];
+  #pragma unroll
+          for (int ho = 0; ho < 8; ++ho) {
+            const float4 w0 = *reinterpret_cast<const float4*>(w + ho * 8), w1 = *reinterpret_cast<const float4*>(w + ho * 8 + 4);
+            o[ho] = b[ho] + w0.x * v[0] + w0.y * v[1] + w0.z * v[2] + w0.w * v[3] + w1.x * v[4] + w1.y * v[5] + w1.z * v[6] + w1.w * v[7];
+          }
+  #pragma unroll
+          for (int h = 0; h < 8; ++h) sp[h * hs] = o[h];
+        } else {
+          float v[16];
+          for (int h = 0; h < H; ++h) v[h] = sp[h * hs];
+          for (int ho = 0; ho < H; ++ho) {
+            float o = b[ho];
+            for (int h = 0; h < H; ++h) o = fmaf(w[ho * H + h], v[h], o);
+            sp[ho * hs] = o;
+          }
         }
-        const float inv = 1.0f / warp_sum(sum);
-        for (int j = lane; j < nk; j += 32) row[j] *= inv;
       }
       __syncthreads();
+      if (pass == 0) {
+        for (int r = warp; r < H * nq; r += kMmaWarps) {
+          float* row = S + (size_t)r * G::SP;
+          float mx = -INFINITY;
+          for (int j = lane; j < nk; j += 32) mx = fmaxf(mx, row[j]);
+          mx = warp_max(mx);
+          float sum = 0.f;
+          for (int j = lane; j < nk; j += 32) {
+            const float e = __expf(row[j] - mx);
+            row[j] = e;
+            sum += e;
+          }
+          const float inv = 1.0f / warp_sum(sum);
+          for (int j = lane; j < nk; j += 32) row[j] *= inv;
+        }
+        __syncthreads();
+      }
     }
   }
   // ---- out = P v (+ v_local), hp heads per pass ----
