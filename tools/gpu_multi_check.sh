@@ -1,4 +1,5 @@
 # 2-GPU box: two-device test, the unmodified reference on the backend, N = 2 bench + reference arm, sharded harness
+export PYTHONPATH=$PWD
 mkdir -p gpurun_out
 python -m pytest tests/test_gpu_two_devices.py -q -m gpu > gpurun_out/t9_two_dev.log 2>&1; tail -3 gpurun_out/t9_two_dev.log
 if [ -d .refcopy ]; then
