@@ -50,6 +50,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200df_head_backward": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "b200df_trunk_ex": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _sz, _vp]),
     "b200df_head_ex": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "b200df_head_static": (_i, [_vp, _vp, _i, _vp, _vp]),
     "b200df_softmax_pack": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "b200df_cam_overlay": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, C.c_float, _vp, _vp]),
     "b200df_threshold_hist": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp]),

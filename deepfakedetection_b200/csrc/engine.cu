@@ -983,6 +983,50 @@ extern "C" int b200df_head_ex(b200df_handle h, const float* a_nchw, const float*
   return head_impl(h, a_nchw, aux, n, logits, stream);
 }
 
+// ---- allocation-free split head (include/b200df.h: b200df_head_static) -----------------------------------------------
+// Same two launches as head_impl's MBConv branch, with the pooled [n, head_c] scratch in a file-scope device array
+// instead of the engine's cudaMalloc'd buffer.  The array's NAME is a host-side stand-in in host code: its device
+// address is looked up with cudaGetSymbolAddress, once per device, with that device current, and cached.
+static __device__ __align__(256) float g_head_static_scratch[B200DF_HEAD_STATIC_MAX_FLOATS];
+static float* g_head_static_ptr[64] = {};
+
+static int head_static_scratch(int device, float** out) {
+  if (device < 0 || device >= 64) return fail(B200DF_E_INVALID, "b200df_head_static: device ordinal %d out of range", device);
+  if (!g_head_static_ptr[device]) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_head_static_scratch);
+    if (e != cudaSuccess || !p)
+      return fail(B200DF_E_CUDA, "b200df_head_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+    g_head_static_ptr[device] = p;
+  }
+  *out = g_head_static_ptr[device];
+  return B200DF_OK;
+}
+
+extern "C" int b200df_head_static(b200df_handle h, const float* a_nchw, int n, float* logits, void* stream) {
+  if (!h || h->precision < 0) return fail(B200DF_E_STATE, "engine not finalized");
+  if (n <= 0) return n == 0 ? B200DF_OK : fail(B200DF_E_INVALID, "negative batch");
+  if (!a_nchw || !logits) return fail(B200DF_E_INVALID, "NULL argument");
+  if (h->net)
+    return fail(B200DF_E_STATE, "b200df_head_static: this architecture's split head (b200df_head_ex) uses no scratch memory");
+  if ((size_t)n * h->head_c > (size_t)B200DF_HEAD_STATIC_MAX_FLOATS)
+    return fail(B200DF_E_INVALID, "b200df_head_static: n * head_c = %d * %d exceeds the static scratch of %d floats",
+                n, h->head_c, (int)B200DF_HEAD_STATIC_MAX_FLOATS);
+  int dev = -1;
+  CU_OK(cudaGetDevice(&dev));
+  if (dev != h->device)
+    return fail(B200DF_E_STATE, "b200df_head_static: current device %d is not the engine's device %d", dev, h->device);
+  float* pooled = nullptr;
+  int rc = head_static_scratch(dev, &pooled);
+  if (rc) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int hw = h->blocks.back().hout * h->blocks.back().hout;
+  // every pooled[n * head_c] element is overwritten before it is read: nothing has to start at zero
+  CU_OK(launch_head_from_nchw(a_nchw, n, hw, h->head_c, h->head_scale, h->head_shift, pooled, s));
+  CU_OK(launch_classifier(pooled, n, h->head_c, h->fc_w, h->fc_b, h->num_classes, logits, s));
+  return B200DF_OK;
+}
+
 extern "C" int b200df_head_backward(b200df_handle h, const float* a_nchw, const float* grad_logits, int n,
                                     float* grad_a_nchw, void* stream) {
   if (!h || h->precision < 0) return fail(B200DF_E_STATE, "engine not finalized");

@@ -133,6 +133,20 @@ int b200df_trunk_ex(b200df_handle h, const float* images, int n, float* a_nchw, 
                     size_t workspace_bytes, void* stream);
 int b200df_head_ex(b200df_handle h, const float* a_nchw, const float* aux, int n, float* logits, void* stream);
 
+/* Allocation-free variant of b200df_head for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  It has NO counterpart in the reference.
+ * b200df_head keeps its pooled [n, head_c] scratch in a per-engine buffer that cudaMalloc grows on demand;
+ * this entry point keeps it in a file-scope `static __device__` array of B200DF_HEAD_STATIC_MAX_FLOATS floats (1.5 MiB,
+ * e.g. 256 images of EfficientNet-B3's 1536 or 307 of B0's 1280 channels) that every GPU loading the library holds until
+ * exit.  It calls no cudaMalloc / cudaFree / allocating library routine; n * head_c beyond the maximum is rejected with
+ * B200DF_E_INVALID, the layer-program architectures (whose split head, b200df_head_ex, uses no scratch) with
+ * B200DF_E_STATE, and a current device other than the engine's with B200DF_E_STATE.  Same results as b200df_head.
+ * ALL calls on a device share the one array, which keeps the last call's contents (every element a call reads it has
+ * written first, so nothing needs clearing): calls that overlap on the GPU -- two streams, two engines, two host
+ * threads -- RACE; serialise them on one stream or use b200df_head. */
+#define B200DF_HEAD_STATIC_MAX_FLOATS (256 * 1536)
+int b200df_head_static(b200df_handle h, const float* a_nchw, int n, float* logits, void* stream);
+
 /* softmax + argmax of [n,num_classes] logits packed as records {p[0..C), pred, label} of
  * (C+2) floats per image -- the buffer the multi-GPU harness all-gathers. labels may be NULL. */
 int b200df_softmax_pack(const float* logits, const int64_t* labels, int n, int num_classes,
