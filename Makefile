@@ -3,7 +3,7 @@ NVCC ?= /usr/local/cuda/bin/nvcc
 SRC_DIR := deepfakedetection_b200/csrc
 OUT := deepfakedetection_b200/libb200df.so
 SRCS := $(SRC_DIR)/engine.cu $(SRC_DIR)/stem.cu $(SRC_DIR)/stem_tc.cu $(SRC_DIR)/dwconv.cu $(SRC_DIR)/dwconv_tma.cu $(SRC_DIR)/se.cu \
-        $(SRC_DIR)/pwconv_simt.cu $(SRC_DIR)/conv3x3.cu $(SRC_DIR)/conv3x3_tc.cu $(SRC_DIR)/attn.cu $(SRC_DIR)/attn_mma.cu $(SRC_DIR)/vit_ops.cu $(SRC_DIR)/pwconv_tc.cu $(SRC_DIR)/tail.cu $(SRC_DIR)/metrics.cu $(SRC_DIR)/overlay.cu
+        $(SRC_DIR)/pwconv_simt.cu $(SRC_DIR)/conv3x3.cu $(SRC_DIR)/conv3x3_tc.cu $(SRC_DIR)/attn.cu $(SRC_DIR)/attn_mma.cu $(SRC_DIR)/vit_ops.cu $(SRC_DIR)/cam_bwd.cu $(SRC_DIR)/pwconv_tc.cu $(SRC_DIR)/tail.cu $(SRC_DIR)/metrics.cu $(SRC_DIR)/overlay.cu
 OBJS := $(SRCS:.cu=.o)
 HDRS := $(wildcard $(SRC_DIR)/*.h) $(wildcard $(SRC_DIR)/*.cuh) $(wildcard $(SRC_DIR)/*.inc) include/b200df.h
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC \

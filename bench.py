@@ -550,6 +550,14 @@ def run_extras(args, model, images, labels, dev, rank, world, local, sync_all, s
                     "frac_of_tensor_peak": round(gflop / 1e3 / (ms / 10 * 1e-3) / float(pk.get("bf16_tflops_sustained", pk["bf16_tflops"])), 4)},
             "kernels": {c: {k2: v[k2] for k2 in ("ms", "launches", "GBps", "TFLOPs")} for c, v in sorted(tab.items(), key=lambda kv: -kv[1]["ms"])},
         }
+        # Grad-CAM on this backbone at configs[2]'s batch (64): EfficientFormerV2's closed form / FasterViT's backward program
+        msc = timed_steps(lambda: m.forward_cam(x64, None), 20, dev, world, local)
+        tabc = class_table(m._engine, lambda: m.forward_cam(x64, None), dev)
+        models[name]["cam"] = {
+            "metric": f"{name}_gradcam_maps_per_s", "value": round(world * 64 * 20 / (msc * 1e-3), 1), "unit": "maps/s",
+            "batch_per_gpu": 64, "ms_per_step": round(msc / 20, 4),
+            "kernels": {c: {k2: v[k2] for k2 in ("ms", "launches", "GBps", "TFLOPs")}
+                        for c, v in sorted(tabc.items(), key=lambda kv: -kv[1]["ms"]) if c.startswith("cam")}}
         del m
         torch.cuda.empty_cache()
     out["models"] = models

@@ -80,7 +80,7 @@ namespace {
 bool is_net_arch(int arch);
 void describe_net(b200df_engine* e);
 int finalize_net(b200df_engine* h, int precision);
-NetWs layout_net_workspace(const b200df_engine* h, int n);
+NetWs layout_net_workspace(const b200df_engine* h, int n, int mode = 0);
 }  // namespace
 
 // ---- EfficientNet-B0 description (timm layout) ---------------------------
@@ -519,10 +519,9 @@ static Workspace layout_workspace(const b200df_engine* h, int n) {
 }
 
 extern "C" int b200df_workspace_bytes(b200df_handle h, int n, int mode, size_t* bytes) {
-  (void)mode;
   if (!h || !bytes || n < 0) return fail(B200DF_E_INVALID, "bad argument");
   if (h->precision < 0) return fail(B200DF_E_STATE, "b200df_finalize has not been called");
-  *bytes = h->net ? layout_net_workspace(h, n > 0 ? n : 1).total : layout_workspace(h, n > 0 ? n : 1).total;
+  *bytes = h->net ? layout_net_workspace(h, n > 0 ? n : 1, mode).total : layout_workspace(h, n > 0 ? n : 1).total;
   return B200DF_OK;
 }
 
@@ -787,8 +786,8 @@ int run_head(b200df_engine* h, int n, uint8_t* ws, const Workspace& W, float* lo
 #include "nets.inc"
 
 namespace {
-int check_net_call(b200df_engine* h, int n, const void* ws, size_t ws_bytes, NetWs* W) {
-  *W = layout_net_workspace(h, n > 0 ? n : 1);
+int check_net_call(b200df_engine* h, int n, const void* ws, size_t ws_bytes, NetWs* W, int mode = 0) {
+  *W = layout_net_workspace(h, n > 0 ? n : 1, mode);
   return check_ws(n, ws, ws_bytes, W->total);
 }
 }  // namespace
@@ -852,10 +851,30 @@ extern "C" int b200df_forward_cam(b200df_handle h, const float* images, int n, c
   if (rc) return rc;
   if (h->net) {
     Net* net = h->net.get();
-    if (!net->wcam)
-      return fail(B200DF_E_STATE, "Grad-CAM for this architecture needs a backward pass through its transformer blocks "
-                                  "(the reference's target rule picks a conv in front of them, web_ui.py:96-105): not built");
+    const bool has_bwd = net->fwd_end >= 0 && (size_t)net->fwd_end < net->ops.size();
+    if (!net->wcam && !has_bwd) return fail(B200DF_E_STATE, "Grad-CAM is not built for this architecture");
     NetWs NW;
+    if (!net->wcam) {
+      // FasterViT: the target activation (global_tokenizer.pos_embed, web_ui.py:94-112) sits in front of the transformer
+      // blocks -> forward program with activation checkpoints, then the backward program (nets.inc, cam_bwd.cu)
+      rc = check_net_call(h, n, workspace, workspace_bytes, &NW, 1);
+      if (rc) return rc;
+      float* lg = logits ? logits : reinterpret_cast<float*>(ws + NW.logits);
+      float* low = cam_lowres ? cam_lowres : reinterpret_cast<float*>(ws + NW.cam_low);
+      CamRun cr;
+      cr.target_cls = target_cls; cr.logits = lg; cr.cam_low = low;
+      rc = run_net(h, images, kInF32NCHW, nullptr, nullptr, n, ws, NW, lg, s, 0, &cr);
+      if (rc) return rc;
+      rc = run_net(h, nullptr, kInF32NCHW, nullptr, nullptr, n, ws, NW, lg, s, 1, &cr);
+      if (rc) return rc;
+      if (cam) {
+        ProfRec* pr = prof_begin(h, s, "cam_upsample", -1, (double)n * (net->feat_side * net->feat_side + (double)h->img * h->img) * 4,
+                                 8.0 * n * h->img * h->img);
+        CU_OK(launch_cam_upsample(low, n, net->feat_side, h->img, cam, s));
+        prof_end(pr, s);
+      }
+      return B200DF_OK;
+    }
     rc = check_net_call(h, n, workspace, workspace_bytes, &NW);
     if (rc) return rc;
     float* lg = logits ? logits : reinterpret_cast<float*>(ws + NW.logits);

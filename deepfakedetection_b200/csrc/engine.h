@@ -72,11 +72,14 @@ struct Workspace {
 };
 
 // ---- layer programs (nets.inc): EfficientFormerV2 / FasterViT ---------------------------------------------------
-enum OpKind { kOpStem = 0, kOpConv3, kOpPw, kOpDw, kOpAttn, kOpLn, kOpUp, kOpWin, kOpCtPool, kOpAddPos, kOpCopyRows, kOpTail };
+enum OpKind { kOpStem = 0, kOpConv3, kOpPw, kOpDw, kOpAttn, kOpLn, kOpUp, kOpWin, kOpCtPool, kOpAddPos, kOpCopyRows, kOpTail,
+              // Grad-CAM: activation checkpoints taken during the forward pass, and the ops of the backward program
+              kOpSave, kOpZero, kOpLnBwd, kOpGeluBwd, kOpAttnBwd, kOpMoveRows, kOpTailBwd, kOpConv3Bwd, kOpCamCt };
 
 struct NetOp {
   int kind = 0;
   char cls[24] = "";            // profiling class
+  bool cam_only = false;        // forward-program op that only runs when a Grad-CAM backward pass follows (kOpSave)
   int in = -1, in2 = -1, in3 = -1, out = -1;   // activation buffer ids
   int i[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   float f[2] = {0.f, 0.f};
@@ -96,7 +99,10 @@ struct Net {
   int stop_after = -1;             // debug: run_net returns after this op (-1 = run everything)
   std::vector<size_t> buf_elems;   // per image
   std::vector<int> buf_f32;
-  std::vector<NetOp> ops;
+  std::vector<NetOp> ops;          // [0, fwd_end): forward program; [fwd_end, size): Grad-CAM backward program (may be empty)
+  int fwd_end = -1;
+  int first_cam_buf = -1;          // buffers >= this id exist only in the mode-1 (forward + CAM) workspace; -1 = none
+  int cam_ntok = 0;                // carrier tokens per image (backward program's last op)
   int a_buf = -1, resid_buf = -1;  // Grad-CAM activation A (raw output of the reference's target conv) / its residual input
   int feat_c = 0, feat_side = 0;
   size_t wcam_off = ~size_t(0);    // arena offset of d logit / d A [num_classes, feat_c] (affine heads only)

@@ -251,6 +251,20 @@ cudaError_t launch_lin_head(const float* a_nchw, const float* aux, int n, int hw
 cudaError_t launch_lin_head_backward(const float* grad_logits, int n, int hw, int c, const float* wcam,
                                      int num_classes, float* grad_a, cudaStream_t s);
 
+// Grad-CAM backward pass of the FasterViT layer program (cam_bwd.cu); tensors in the engine dtype, fp32 math
+cudaError_t launch_layernorm_bwd(const void* x, const float* gamma, const void* dy, const void* res, void* out,
+                                 long long rows, int c, float eps, int dtype, cudaStream_t s);
+cudaError_t launch_gelu_bwd(const void* pre, void* g, long long total, int dtype, cudaStream_t s);
+cudaError_t launch_move_rows(void* src, void* dst, long long nseq, int src_rows, int src_off, int dst_rows, int dst_off,
+                             int nrows, int c, int dtype, cudaStream_t s);
+cudaError_t launch_tail_bwd(const float* n_scale, const float* w, int n, int hw, int c, int num_classes,
+                            const int32_t* target_cls, const float* logits, void* g, int dtype, cudaStream_t s);
+cudaError_t launch_cam_from_ct_grad(const void* a, const void* gct, int n, int hw, int c, int ntok, float* cam_lowres,
+                                    int dtype, cudaStream_t s);
+cudaError_t launch_conv3x3_s2_bwd(const void* dy, const void* w, void* dx, int n, int hin, int cin, int cinp, int cout,
+                                  int dtype, cudaStream_t s);
+cudaError_t launch_attention_bwd(const AttnArgs& a, const void* dout, void* dq, void* dk, void* dv, int dtype, cudaStream_t s);
+
 // on-device metrics tail (metrics.cu)
 // Grad-CAM overlay (overlay.cu): de-normalise + JET heat map + blend + max-normalise -> uint8 HWC
 cudaError_t launch_cam_overlay(const float* x_nchw, const float* cam, int n, int h, int w, int denorm, const float* mean,

@@ -54,7 +54,7 @@ class Engine:
         self.feature_channels, self.feature_side = int(ch.value), int(side.value)  # Grad-CAM activation A
         self.precision: int | None = None
         # workspaces keyed by (batch size, stream): two forwards of the same n on different streams never share scratch
-        self._ws: "collections.OrderedDict[tuple[int, int], tuple[torch.Tensor, int, int]]" = collections.OrderedDict()
+        self._ws: "collections.OrderedDict[tuple[int, int], tuple[torch.Tensor, int, int, int]]" = collections.OrderedDict()
         self._lock = threading.Lock()
         # CUDA-graph replay for small batches (launch-bound regime: the UI's n = 1, strong scaling's 32 images per GPU):
         # one graph per batch size, captured on first use; B200DF_GRAPH_MAX_N=0 disables it
@@ -91,25 +91,30 @@ class Engine:
     # -- workspace -----------------------------------------------------------------------------------
     def _drop_workspaces(self) -> None:
         cur = torch.cuda.current_stream(self.device)
-        for buf, _base, _size in self._ws.values():
+        for buf, _base, _size, _mode in self._ws.values():
             buf.record_stream(cur)   # kernels launched on another stream may still be using it
         self._ws.clear()
         self._graphs.clear()
 
-    def _workspace(self, n: int, stream_id: int | None = None) -> tuple[int, int]:
+    def _workspace(self, n: int, stream_id: int | None = None, mode: int = 0) -> tuple[int, int]:
+        """mode 0: forward; mode 1: forward + Grad-CAM (a superset: FasterViT's CAM adds checkpoint / gradient buffers)."""
         if stream_id is None:
             stream_id = torch.cuda.current_stream(self.device).cuda_stream
         key = (n, stream_id)
         hit = self._ws.get(key)
+        if hit is not None and hit[3] < mode:      # a forward-only workspace cannot serve a CAM call: replace it
+            hit[0].record_stream(torch.cuda.current_stream(self.device))
+            del self._ws[key]
+            hit = None
         if hit is None:
             need = C.c_size_t()
-            _lib.check(self._lib.b200df_workspace_bytes(self._h, n, 1, C.byref(need)))
+            _lib.check(self._lib.b200df_workspace_bytes(self._h, n, mode, C.byref(need)))
             buf = torch.empty(int(need.value) + _ALIGN, dtype=torch.uint8, device=self.device)
             base = (buf.data_ptr() + _ALIGN - 1) // _ALIGN * _ALIGN
             while len(self._ws) >= 6:  # a few (batch size, stream) pairs: full batch, ragged tail, n = 1 from the UI ...
-                _k, (old, _b, _s) = self._ws.popitem(last=False)   # least recently used
-                old.record_stream(torch.cuda.current_stream(self.device))
-            hit = (buf, base, int(need.value))
+                _k, old = self._ws.popitem(last=False)   # least recently used
+                old[0].record_stream(torch.cuda.current_stream(self.device))
+            hit = (buf, base, int(need.value), mode)
             self._ws[key] = hit
         else:
             self._ws.move_to_end(key)
@@ -202,7 +207,7 @@ class Engine:
         if targets is not None:
             tgt = targets.to(device=dev, dtype=torch.int32).contiguous()
         with self._lock, torch.cuda.device(dev):
-            base, size = self._workspace(n)
+            base, size = self._workspace(n, mode=1)
             _lib.check(self._lib.b200df_forward_cam(self._h, _ptr(images), n, _ptr(tgt), _ptr(logits), _ptr(low),
                                                    _ptr(cam), C.c_void_p(base), size, _stream_ptr(dev)))
         return logits, low, cam

@@ -116,7 +116,8 @@ class B200Module(nn.Module):
     arch_id = -1
     arch_name = ""
     default_image_size = 224
-    supports_cam = True
+    supports_cam = True          # fused Grad-CAM (forward_cam / the gradcam.GradCAM front)
+    supports_cam_hooks = True    # pytorch-grad-cam's hook protocol (forward with grad enabled: trunk -> A -> head)
 
     def __init__(self, num_classes: int = 2, precision: str = "bf16") -> None:
         super().__init__()
@@ -207,11 +208,12 @@ class B200Module(nn.Module):
             # Grad-CAM hook protocol (web_ui.py:275-279): pytorch-grad-cam hooks `_conv_head` and calls
             # `.register_hook` on its output, so A must be a graph leaf that requires grad.  The trunk has no
             # backward (inference engine): gradients stop at A, which is all Grad-CAM needs.
-            if not self.supports_cam:
+            if not self.supports_cam_hooks:
                 raise NotImplementedError(
                     f"b200 {self.arch_name}: the reference's Grad-CAM target rule (web_ui.py:96-105) picks a conv in front of "
-                    "this network's transformer blocks, so Grad-CAM needs a backward pass through them, which this "
-                    "inference engine does not have.  Call the model under torch.inference_mode()/no_grad().")
+                    "this network's transformer blocks; the backward pass through them exists only inside the fused "
+                    "forward_cam() / deepfakedetection_b200.gradcam.GradCAM(use_hooks=False) path, not as an autograd graph.  "
+                    "Call the model under torch.inference_mode()/no_grad().")
             a, aux = ops.trunk(images.detach(), self._engine_id)
             a = self._cam_point()(a.requires_grad_(True))
             return ops.head(a, aux, self._engine_id)

@@ -297,9 +297,14 @@ _FV_CFG = {
 
 
 class B200FasterViT(B200Module):
-    """Drop-in for ``fastervit.create_model("faster_vit_0_224" | "faster_vit_2_224")`` + ``head = nn.Linear(...)``."""
+    """Drop-in for ``fastervit.create_model("faster_vit_0_224" | "faster_vit_2_224")`` + ``head = nn.Linear(...)``.
 
-    supports_cam = False
+    Grad-CAM: the reference's target rule (web_ui.py:94-112) picks ``levels.2.global_tokenizer.pos_embed``; the fused
+    ``forward_cam`` runs the engine's backward program through every block behind it (csrc/cam_bwd.cu).  The map is
+    14x14 before the upsample.  The hook protocol (forward with grad enabled) is not offered: there is no autograd graph."""
+
+    supports_cam = True
+    supports_cam_hooks = False
 
     def __init__(self, num_classes: int = 2, precision: str = "bf16", variant: str = "faster_vit_0_224") -> None:
         if variant not in _FV_CFG:
@@ -330,9 +335,3 @@ class B200FasterViT(B200Module):
 
     def _cam_point(self) -> nn.Module:
         return self.levels[2].global_tokenizer.pos_embed
-
-    @torch.no_grad()
-    def forward_cam(self, images: torch.Tensor, targets: torch.Tensor | None = None):
-        raise NotImplementedError(
-            f"b200 {self.arch_name}: Grad-CAM on the reference's target layer (levels.2.global_tokenizer.pos_embed, "
-            "web_ui.py:96-105) needs a backward pass through 11 transformer blocks; not built (SURVEY.md 8f-4).")

@@ -41,6 +41,29 @@ def postprocess_cam(cam_lowres: torch.Tensor, out_hw: tuple[int, int]) -> torch.
     return _minmax(cam)
 
 
+def gradcam_on_layer(model, target: torch.nn.Module, images: torch.Tensor, targets: torch.Tensor):
+    """Hook-and-backward Grad-CAM on an explicit target layer (pytorch-grad-cam's mechanism): the route for the networks
+    whose target -- the last ``nn.Conv2d`` in ``modules()`` order, /root/reference/web_ui.py:94-112 -- is not the conv head.
+    Returns (logits [N,C], cam_lowres [N,h,w] after ReLU, cam [N,H,W] in [0,1], A [N,K,h,w], G [N,K,h,w])."""
+    store = {}
+
+    def hook(_m, _inp, out):
+        store["A"] = out
+        out.register_hook(lambda g: store.__setitem__("G", g))
+
+    handle = target.register_forward_hook(hook)
+    try:
+        with torch.enable_grad():
+            model.zero_grad(set_to_none=True)
+            logits = model(images)
+            logits[torch.arange(images.shape[0]), targets].sum().backward()
+    finally:
+        handle.remove()
+    a, g = store["A"].detach(), store["G"].detach()
+    cam_low = (g.mean((2, 3), keepdim=True) * a).sum(1).clamp_min(0)
+    return logits.detach(), cam_low, postprocess_cam(cam_low, tuple(images.shape[-2:])), a, g
+
+
 def gradcam_autograd(model, images: torch.Tensor, targets: torch.Tensor):
     """Hook-and-backward Grad-CAM on the layer the reference's target rule picks (/root/reference/web_ui.py:108-110):
     ``model._conv_head`` when it exists (efficientnet_pytorch layout), else ``model.conv_head`` (timm layout).

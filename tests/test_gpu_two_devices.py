@@ -33,7 +33,7 @@ def test_forward_and_hook_gradcam_on_cuda0_then_cuda1(name, oracle_mod):
         assert out.device == torch.device(dev)
         outs.append(out.cpu())
         assert (out.cpu().softmax(1) - ref.softmax(1)).abs().max().item() <= 2e-2
-        if model.supports_cam:   # the hook protocol allocates the per-engine head scratch on THIS device
+        if model.supports_cam_hooks:   # the hook protocol allocates the per-engine head scratch on THIS device
             with GradCAM(model=model, target_layers=[model._cam_point()], use_hooks=True) as cam:
                 gray = cam(input_tensor=x[:1].to(dev), targets=[ClassifierOutputTarget(int(ref[0].argmax()))])[0]
             assert gray.shape == (224, 224) and 0.0 <= float(gray.min()) and float(gray.max()) <= 1.0 + 1e-6
