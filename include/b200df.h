@@ -111,8 +111,12 @@ int b200df_forward_u8(b200df_handle h, const uint8_t* images_hwc, int n, const f
                       void* stream);
 
 /* Forward + Grad-CAM in one pass.  target_cls: int32 [n] device (NULL = argmax of logits).
- * cam_lowres: float32 [n,7,7] (ReLU'd, unnormalised) or NULL; cam: float32 [n,224,224]
- * in [0,1] (min-max, bilinear upsample, min-max) or NULL. */
+ * cam_lowres: float32 [n,s,s] (ReLU'd, unnormalised; s = b200df_feature_shape's side: 7, FasterViT 14) or NULL;
+ * cam: float32 [n,224,224] in [0,1] (min-max, bilinear upsample, min-max) or NULL.  The workspace must be sized with
+ * mode 1.  The target layer is the one the reference's rule picks (web_ui.py:94-112): conv_head / _conv_head
+ * (EfficientNet, closed form), stages.3.blocks.5.mlp.fc2.conv (EfficientFormerV2, closed form),
+ * levels.2.global_tokenizer.pos_embed (FasterViT: forward with activation checkpoints, then a backward pass through the
+ * transformer blocks behind it -- csrc/cam_bwd.cu). */
 int b200df_forward_cam(b200df_handle h, const float* images, int n, const int32_t* target_cls,
                        float* logits, float* cam_lowres, float* cam, void* workspace,
                        size_t workspace_bytes, void* stream);
@@ -128,7 +132,8 @@ int b200df_head_backward(b200df_handle h, const float* a_nchw, const float* grad
 /* Same split with an auxiliary per-image term, aux float32 [n,num_classes]: EfficientFormerV2's Grad-CAM target
  * (the last nn.Conv2d, `stages.3.blocks.5.mlp.fc2.conv`, web_ui.py:96-105) is followed by an AFFINE map whose offset
  * depends on the block's residual input, not on A: trunk_ex writes aux = logits - lin(A), head_ex(A, aux) = aux + lin(A).
- * The EfficientNet engines write / ignore zeros.  FasterViT has no split path (B200DF_E_STATE). */
+ * The EfficientNet engines write / ignore zeros.  FasterViT has no split path (B200DF_E_STATE): its Grad-CAM is
+ * served by b200df_forward_cam only. */
 int b200df_trunk_ex(b200df_handle h, const float* images, int n, float* a_nchw, float* aux, void* workspace,
                     size_t workspace_bytes, void* stream);
 int b200df_head_ex(b200df_handle h, const float* a_nchw, const float* aux, int n, float* logits, void* stream);

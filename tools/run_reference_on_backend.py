@@ -177,10 +177,10 @@ def main() -> int:
 
     # ---- web_ui.predict_and_visualize, unmodified (import builds the interface from config/inference.yaml in CWD) ----
     if args.ui:
-        # web_ui loops over every selected model and runs GradCAM on each (web_ui.py:250-283): the UI config holds the
-        # models whose Grad-CAM the backend serves; FasterViT's refusal is shown separately below
+        # web_ui loops over every selected model and runs GradCAM on each (web_ui.py:250-283) -- FasterViT included: its target
+        # (levels.2.global_tokenizer.pos_embed) is served by the engine's backward program
         (work / "config").mkdir(exist_ok=True)
-        ui_models = [m for m in models if not m.startswith("faster_vit")]
+        ui_models = list(models)
         (work / "config" / "inference.yaml").write_text(write_config(work, ui_models, args.batch).read_text())
         ui = importlib.import_module("web_ui")
         from PIL import Image
@@ -194,15 +194,6 @@ def main() -> int:
             print(f"  CAM target of {b.name}: {names.get(id(b.target_layer), type(b.target_layer).__name__)}")
         assert panel.ndim == 3 and panel.shape[2] == 3 and panel.dtype == np.uint8
         assert panel.shape[1] == 2 * 224 * len(ui_models), "one 224-pixel panel per model, exported at 2x"
-        fv = [m for m in models if m.startswith("faster_vit")]
-        if fv:
-            (work / "config" / "inference.yaml").write_text(write_config(work, fv[:1], args.batch).read_text())
-            ui.initialize_from_config(work / "config" / "inference.yaml")
-            try:
-                ui.predict_and_visualize(img)
-                print("FasterViT Grad-CAM: unexpectedly served")
-            except NotImplementedError as ex:
-                print("FasterViT through web_ui: forward OK, Grad-CAM refused as documented ->", str(ex)[:120])
     print(f"{bad} model(s) out of tolerance; work dir {work}")
     return 1 if bad else 0
 
