@@ -112,31 +112,31 @@ cudaError_t launch_layernorm(const void* x, void* y, const float* gamma, const f
 
 // ---- bilinear x2 upsample (align_corners = False) + activation -------------------------------------------------
 // dst index d -> src = max((d + 0.5) / 2 - 0.5, 0); i0 = floor(src), i1 = min(i0 + 1, side - 1), frac = src - i0.
+// One CTA per (image, output row): the row's two source rows and the y weight are fixed, all index math is 32-bit
+// (the flat 64-bit index with three runtime divisions per 8 outputs made the first version issue-bound at 85 us).
 template <typename T>
 __global__ void __launch_bounds__(256)
-upsample2x_act_kernel(const T* __restrict__ x, T* __restrict__ y, int n, int side, int C, int act) {
+upsample2x_act_kernel(const T* __restrict__ x, T* __restrict__ y, int side, int C, int act) {
   const int C8 = C >> 3, os = side * 2;
-  const long long total = (long long)n * os * os * C8;
+  const int oy = blockIdx.x % os, img = blockIdx.x / os;
+  const float sy = fmaxf((oy + 0.5f) * 0.5f - 0.5f, 0.f);
+  const int y0 = (int)sy, y1 = min(y0 + 1, side - 1);
+  const float fy = sy - (float)y0;
+  const T* r0 = x + ((size_t)img * side + y0) * side * C;
+  const T* r1 = x + ((size_t)img * side + y1) * side * C;
+  T* out = y + ((size_t)img * os + oy) * os * C;
   griddep_wait();
   griddep_launch_dependents();
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(idx % C8);
-    long long r = idx / C8;
-    const int ox = (int)(r % os);
-    r /= os;
-    const int oy = (int)(r % os);
-    const int img = (int)(r / os);
-    const float sy = fmaxf((oy + 0.5f) * 0.5f - 0.5f, 0.f), sx = fmaxf((ox + 0.5f) * 0.5f - 0.5f, 0.f);
-    const int y0 = (int)sy, x0 = (int)sx;
-    const int y1 = min(y0 + 1, side - 1), x1 = min(x0 + 1, side - 1);
-    const float fy = sy - (float)y0, fx = sx - (float)x0;
-    const T* base = x + (size_t)img * side * side * C + c8 * 8;
+  for (int i = threadIdx.x; i < os * C8; i += blockDim.x) {
+    const int ox = i / C8, c8 = i - ox * C8;
+    const float sx = fmaxf((ox + 0.5f) * 0.5f - 0.5f, 0.f);
+    const int x0 = (int)sx, x1 = min(x0 + 1, side - 1);
+    const float fx = sx - (float)x0;
     float a[8], b[8], c[8], d[8], o[8];
-    load8<T>(base + ((size_t)y0 * side + x0) * C, a);
-    load8<T>(base + ((size_t)y0 * side + x1) * C, b);
-    load8<T>(base + ((size_t)y1 * side + x0) * C, c);
-    load8<T>(base + ((size_t)y1 * side + x1) * C, d);
+    load8<T>(r0 + x0 * C + c8 * 8, a);
+    load8<T>(r0 + x1 * C + c8 * 8, b);
+    load8<T>(r1 + x0 * C + c8 * 8, c);
+    load8<T>(r1 + x1 * C + c8 * 8, d);
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       // torch's order: interpolate along x within each row, then along y
@@ -144,21 +144,20 @@ upsample2x_act_kernel(const T* __restrict__ x, T* __restrict__ y, int n, int sid
       const float bot = c[e] * (1.f - fx) + d[e] * fx;
       o[e] = apply_act<is_bf16<T>::value>(top * (1.f - fy) + bot * fy, act);
     }
-    store8<T>(y + idx * 8, o);
+    store8<T>(out + (size_t)i * 8, o);
   }
 }
 
 cudaError_t launch_upsample2x_act(const void* x, void* y, int n, int side, int c, int act, int dtype, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   if (c % 8) return cudaErrorInvalidValue;
-  const long long total = (long long)n * side * side * 4 * (c / 8);
-  const unsigned grid = (unsigned)std::min<long long>((total + 255) / 256, (long long)kNumSMs * 16);
+  const unsigned grid = (unsigned)(n * side * 2);
   count_launch();
   if (dtype == kBF16)
     return launch_pdl(upsample2x_act_kernel<bf16>, dim3(grid), dim3(256), 0, s, reinterpret_cast<const bf16*>(x),
-                      reinterpret_cast<bf16*>(y), n, side, c, act);
+                      reinterpret_cast<bf16*>(y), side, c, act);
   return launch_pdl(upsample2x_act_kernel<float>, dim3(grid), dim3(256), 0, s, reinterpret_cast<const float*>(x),
-                    reinterpret_cast<float*>(y), n, side, c, act);
+                    reinterpret_cast<float*>(y), side, c, act);
 }
 
 // ---- window partition / reverse ----------------------------------------------------------------------------------
