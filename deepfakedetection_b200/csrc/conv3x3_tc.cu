@@ -11,6 +11,12 @@
 //     box [64 ch, 8, TH, TI] at (c0, ox0*s + kx - 1, oy0*s + ky - 1, img0), traversal stride s in W and H,
 // which lands in shared memory as exactly the 128-row x 128-byte, 128B-swizzled K-major tile tcgen05.mma wants; the
 // conv's zero padding, ragged image edges, ragged batches and channel tails are the TMA unit's out-of-bounds zero fill.
+// Stride-1 layers (the FasterViT ConvBlocks) run in "vertical halo" mode: the tile is 8 wide x 16 tall in ONE image and a
+// pipeline stage is (channel chunk, kernel column kx): ONE A box of 18 rows feeds the three taps ky = 0..2 -- a shift by one
+// image row of an 8-pixel-wide tile is exactly one 1024-byte swizzle atom, i.e. a legal start address for the UMMA
+// descriptor -- so the activation operand crosses L2 -> shared memory 3 times instead of 9 (the kernel is bound by that
+// traffic: 216 KB per 128 x 64 x 576 tile at C = 64 is 27 KB/clk chip-wide at full tensor rate against ~6 KB/clk of L2).
+// When all weights fit (cout_pad == bn and 9 * cpt tiles <= 80 KB: C = 64, 96) they are loaded ONCE per CTA and stay.
 // The pipeline is the one of pwconv_tc.cu: a TMA producer warp, a multi-stage mbarrier ring, one MMA-issuing lane
 // (M=128, N<=256, K=16 per instruction) into a double-buffered TMEM accumulator, and two groups of epilogue warps
 // (tcgen05.ld -> bias -> GELU/ReLU -> +residual -> bf16 -> swizzled staging -> 4-D TMA store, edges clipped).
@@ -62,15 +68,19 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int b_bytes = p.bn * kCBK * 2;
-  const int stage_bytes = kCABytes + b_bytes;
-  uint8_t* epi_smem = smem + (size_t)p.stages * stage_bytes;
+  const int a_bytes = p.vhalo ? (p.th + 2) * 1024 : kCABytes;
+  const int res_bytes = p.b_res ? p.k_chunks * b_bytes : 0;                       // resident weights in front of the ring
+  const int stage_bytes = a_bytes + (p.b_res ? 0 : (p.vhalo ? 3 : 1) * b_bytes);
+  uint8_t* ring = smem + res_bytes;
+  uint8_t* epi_smem = ring + (size_t)p.stages * stage_bytes;
   float* sbias = reinterpret_cast<float*>(epi_smem + kCEpiWarps * kCEpiStageBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(sbias + kCMaxBias);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kCMaxStages;
   uint64_t* tmem_full = bars + 2 * kCMaxStages;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* bres_bar = tmem_empty + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bres_bar + 1);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int t_begin = blockIdx.x, t_end = p.num_tiles, t_step = gridDim.x;
@@ -97,6 +107,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
       mbar_init(&tmem_full[a], 1);
       mbar_init(&tmem_empty[a], 256);
     }
+    mbar_init(bres_bar, 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -115,18 +126,43 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     // ================= TMA producer =================
     int s = 0;
     uint32_t ph = 0;
-    for (int t = t_begin; t < t_end; t += t_step) {
+    if (p.b_res && t_begin < t_end) {   // all weight tiles, once (weights only: no dependence on the previous kernel's output)
+      if (elect_one()) {
+        mbar_arrive_expect_tx(bres_bar, (uint32_t)res_bytes);
+        for (int kc = 0; kc < p.k_chunks; ++kc) tma_load_2d(smem + (size_t)kc * b_bytes, &tmap_w, kc * kCBK, 0, bres_bar);
+      }
+      __syncwarp();
+    }
+    for (int t = t_begin; p.vhalo && t < t_end; t += t_step) {
+      const TileCoord tc_ = decode(t);
+      const int ix0 = tc_.tx * 8 - 1, iy0 = tc_.ty * p.th - 1;
+      for (int cc = 0; cc < p.cpt; ++cc)
+        for (int kx = 0; kx < 3; ++kx) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          uint8_t* sa = ring + (size_t)s * stage_bytes;
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&full_bar[s], (uint32_t)stage_bytes);
+            tma_load_4d(sa, &tmap_x, cc * kCBK, ix0 + kx, iy0, tc_.g, &full_bar[s]);   // th + 2 rows: taps ky = 0, 1, 2
+            if (!p.b_res)
+              for (int ky = 0; ky < 3; ++ky)
+                tma_load_2d(sa + a_bytes + ky * b_bytes, &tmap_w, ((ky * 3 + kx) * p.cpt + cc) * kCBK, tc_.nt * p.bn, &full_bar[s]);
+          }
+          __syncwarp();
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+    }
+    for (int t = t_begin; !p.vhalo && t < t_end; t += t_step) {
       const TileCoord tc_ = decode(t);
       const int ix0 = tc_.tx * 8 * p.stride - 1, iy0 = tc_.ty * p.th * p.stride - 1, img0 = tc_.g * p.ti;
       for (int kc = 0; kc < p.k_chunks; ++kc) {
         const int tap = kc / p.cpt, cc = kc - tap * p.cpt;
         const int ky = tap / 3, kx = tap - ky * 3;
         mbar_wait(&empty_bar[s], ph ^ 1);
-        uint8_t* sa = smem + (size_t)s * stage_bytes;
+        uint8_t* sa = ring + (size_t)s * stage_bytes;
         if (elect_one()) {
           mbar_arrive_expect_tx(&full_bar[s], (uint32_t)stage_bytes);
           tma_load_4d(sa, &tmap_x, cc * kCBK, ix0 + kx, iy0 + ky, img0, &full_bar[s]);
-          tma_load_2d(sa + kCABytes, &tmap_w, kc * kCBK, tc_.nt * p.bn, &full_bar[s]);
+          if (!p.b_res) tma_load_2d(sa + kCABytes, &tmap_w, kc * kCBK, tc_.nt * p.bn, &full_bar[s]);
         }
         __syncwarp();
         if (++s == p.stages) { s = 0; ph ^= 1; }
@@ -135,12 +171,46 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   } else if (warp == 1) {
     // ================= MMA issuer =================
     const uint32_t idesc = make_idesc_bf16_m128((uint32_t)p.bn);
-    const uint64_t desc0 = make_sw128_kmajor_desc(smem_u32(smem));
+    const uint64_t desc_res = make_sw128_kmajor_desc(smem_u32(smem));
+    const uint64_t desc0 = make_sw128_kmajor_desc(smem_u32(ring));
     const int stage16 = stage_bytes >> 4;
     int s = 0;
     uint32_t ph = 0;
     int lt = 0;
-    for (int t = t_begin; t < t_end; t += t_step, ++lt) {
+    if (p.b_res && t_begin < t_end) {
+      mbar_wait(bres_bar, 0);
+      tcgen05_fence_after();
+    }
+    for (int t = t_begin; p.vhalo && t < t_end; t += t_step, ++lt) {
+      const int acc = lt & 1;
+      const uint32_t acc_ph = (lt >> 1) & 1;
+      mbar_wait(&tmem_empty[acc], acc_ph ^ 1);
+      tcgen05_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride);
+      for (int cc = 0; cc < p.cpt; ++cc) {
+        const int crem = p.cin - cc * kCBK;
+        const int nk = crem >= kCBK ? 4 : ((crem + 15) >> 4);
+        for (int kx = 0; kx < 3; ++kx) {
+          mbar_wait(&full_bar[s], ph);
+          tcgen05_fence_after();
+          const uint64_t da0 = desc0 + (uint64_t)(uint32_t)(s * stage16);
+          if (elect_one()) {
+            for (int ky = 0; ky < 3; ++ky) {
+              const uint64_t da = da0 + (uint64_t)(ky * (1024 >> 4));          // one image row of the tile = one swizzle atom
+              const uint64_t db = p.b_res ? desc_res + (uint64_t)(uint32_t)((((ky * 3 + kx) * p.cpt + cc) * b_bytes) >> 4)
+                                          : da0 + (uint64_t)(uint32_t)((a_bytes + ky * b_bytes) >> 4);
+              for (int k = 0; k < nk; ++k)
+                umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (cc | kx | ky | k) ? 1u : 0u);
+            }
+            umma_commit(&empty_bar[s]);
+            if (cc == p.cpt - 1 && kx == 2) umma_commit(&tmem_full[acc]);
+          }
+          __syncwarp();
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+    for (int t = t_begin; !p.vhalo && t < t_end; t += t_step, ++lt) {
       const int acc = lt & 1;
       const uint32_t acc_ph = (lt >> 1) & 1;
       mbar_wait(&tmem_empty[acc], acc_ph ^ 1);
@@ -150,7 +220,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
         mbar_wait(&full_bar[s], ph);
         tcgen05_fence_after();
         const uint64_t da = desc0 + (uint64_t)(uint32_t)(s * stage16);
-        const uint64_t db = da + (uint64_t)(kCABytes >> 4);
+        const uint64_t db = p.b_res ? desc_res + (uint64_t)(uint32_t)((kc * b_bytes) >> 4) : da + (uint64_t)(kCABytes >> 4);
         const int cc = kc % p.cpt;
         const int crem = p.cin - cc * kCBK;                       // valid channels of this chunk
         const int nk = crem >= kCBK ? 4 : ((crem + 15) >> 4);     // K = 16 steps that hold any non-zero column
@@ -268,9 +338,19 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 
 // ---- host side ---------------------------------------------------------------------------------------------------
 
-static size_t conv_tc_smem(int bn, int stages) {
-  return 1024 + (size_t)stages * (kCABytes + bn * kCBK * 2) + kCEpiWarps * kCEpiStageBytes + kCMaxBias * sizeof(float) +
-         (2 * kCMaxStages + 4) * sizeof(uint64_t) + 16;
+static size_t conv_tc_smem(int bn, int stages, size_t stage_bytes = 0, size_t res_bytes = 0) {
+  if (!stage_bytes) stage_bytes = kCABytes + (size_t)bn * kCBK * 2;
+  return 1024 + res_bytes + (size_t)stages * stage_bytes + kCEpiWarps * kCEpiStageBytes + kCMaxBias * sizeof(float) +
+         (2 * kCMaxStages + 5) * sizeof(uint64_t) + 16;
+}
+
+static bool conv_vhalo_enabled() {   // B200DF_CONV_VHALO=0: the one-box-per-tap schedule everywhere (A/B aid)
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200DF_CONV_VHALO");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
 }
 
 int conv3x3_tc_cin_pad(int cin) { return (cin + kCBK - 1) / kCBK * kCBK; }
@@ -291,6 +371,9 @@ int plan_conv3x3_tc(Conv3Plan& plan, const void* x, int n, int h, int w, int cin
     const double eff = (double)Ho / ((Ho + th - 1) / th * th) * (double)n / ((n + ti - 1) / ti * ti);
     if (eff > best_eff + 1e-9) { best_eff = eff; best_th = th; }
   }
+  // stride 1: vertical-halo schedule (16-row tiles of ONE image; a few wasted rows at 56 / 28 buy 2.7x less A traffic)
+  p.vhalo = (stride == 1 && conv_vhalo_enabled()) ? 1 : 0;
+  if (p.vhalo) best_th = 16;
   p.cin = cin; p.cout = cout; p.cout_pad = cout_pad; p.bn = bn;
   p.Ho = Ho; p.Wo = Wo; p.stride = stride; p.n_img = n;
   p.th = best_th; p.ti = 16 / best_th;
@@ -307,19 +390,24 @@ int plan_conv3x3_tc(Conv3Plan& plan, const void* x, int n, int h, int w, int cin
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * p.acc_stride)) cols <<= 1;
   p.tmem_cols = cols;
+  const size_t b_bytes = (size_t)bn * kCBK * 2;
+  p.b_res = (p.vhalo && p.n_tiles == 1 && p.k_chunks * b_bytes <= 80 * 1024) ? 1 : 0;
+  const size_t res_bytes = p.b_res ? p.k_chunks * b_bytes : 0;
+  const size_t stage_bytes = p.vhalo ? (size_t)(p.th + 2) * 1024 + (p.b_res ? 0 : 3 * b_bytes) : kCABytes + b_bytes;
   int stages = kCMaxStages;
-  while (stages > 2 && conv_tc_smem(bn, stages) > 220 * 1024) --stages;
+  while (stages > 2 && conv_tc_smem(bn, stages, stage_bytes, res_bytes) > 220 * 1024) --stages;
+  if (conv_tc_smem(bn, stages, stage_bytes, res_bytes) > 220 * 1024) return -1;
   p.stages = stages;
   p.bias = bias;
   p.residual = reinterpret_cast<const bf16*>(residual);
   plan.act = act;
-  plan.smem = conv_tc_smem(bn, stages);
+  plan.smem = conv_tc_smem(bn, stages, stage_bytes, res_bytes);
   plan.grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
   // A: NHWC activations [cin, w, h, n], box [64, 8 s, th s, ti] traversed with stride s in W and H, 128B swizzle
   {
     unsigned long long dims[4] = {(unsigned long long)cin, (unsigned long long)w, (unsigned long long)h, (unsigned long long)n};
     unsigned long long str[4] = {2, (unsigned long long)cin * 2, (unsigned long long)w * cin * 2, (unsigned long long)h * w * cin * 2};
-    unsigned box[4] = {(unsigned)kCBK, (unsigned)(8 * stride), (unsigned)(p.th * stride), (unsigned)p.ti};
+    unsigned box[4] = {(unsigned)kCBK, (unsigned)(8 * stride), (unsigned)(p.vhalo ? p.th + 2 : p.th * stride), (unsigned)p.ti};
     unsigned es[4] = {1, (unsigned)stride, (unsigned)stride, 1};
     if (encode_tmap_nd_bf16(plan.tmap_x, x, 4, dims, str, box, 128, es)) return -3;
   }

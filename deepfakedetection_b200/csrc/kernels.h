@@ -188,6 +188,9 @@ struct ConvTcParams {
   int cpt, k_chunks;              // 64-channel chunks per tap, 9 * cpt
   int n_tiles, num_tiles, stages, acc_stride;
   uint32_t tmem_cols;
+  // vhalo (stride 1, th 16, ti 1): one A box of th + 2 rows serves the three taps of a kernel COLUMN (a row shift of the
+  // 8-pixel-wide tile is one 1024-byte swizzle atom); b_res: all 9 * cpt weight tiles stay in shared memory (cout_pad == bn)
+  int vhalo, b_res;
   const float* bias;
   const __nv_bfloat16* residual;
 };

@@ -86,6 +86,76 @@ layernorm_kernel(const T* __restrict__ x, T* __restrict__ y, const float* __rest
   }
 }
 
+// C <= 128 (FasterViT's level-0 / level-1 downsample norms, C = 64 .. 192 / 2): a row is only C / 8 <= 16 vectors, so a warp
+// takes 32 / LPR rows at once, LPR lanes each (the full-warp kernel above left 16-24 lanes idle: 183 us for the 56 x 56 x 64
+// norm of FasterViT-0 against 25 us of HBM time).  R such row groups per warp; reductions stay inside the LPR-lane group.
+template <typename T, int LPR, int R>
+__global__ void __launch_bounds__(256)
+layernorm_small_kernel(const T* __restrict__ x, T* __restrict__ y, const float* __restrict__ gamma,
+                       const float* __restrict__ beta, long long rows, int C, float eps) {
+  constexpr int RPW = 32 / LPR;                     // rows per warp pass
+  const int lane = threadIdx.x & 31, sub = lane / LPR, vi = lane % LPR;
+  const long long warp_id = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long row0 = warp_id * (RPW * R) + sub;
+  const int nv = C >> 3;
+  const bool act = vi < nv;
+  griddep_wait();
+  griddep_launch_dependents();
+  float v[R][8];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const long long row = row0 + (long long)r * RPW;
+    if (act && row < rows) {
+      load8<T>(x + row * C + vi * 8, v[r]);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[r][e] = 0.f;
+    }
+  }
+  float g[8], b[8];
+  if (act) {
+    load8<float>(gamma + vi * 8, g);
+    load8<float>(beta + vi * 8, b);
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const long long row = row0 + (long long)r * RPW;
+    float sum = 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sum += v[r][e];
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float mean = sum / (float)C;
+    float sq = 0.f;
+    if (act) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float d = v[r][e] - mean;
+        sq = fmaf(d, d, sq);
+      }
+    }
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    const float rstd = 1.0f / sqrtf(sq / (float)C + eps);
+    if (act && row < rows) {
+      float o8[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o8[e] = fmaf((v[r][e] - mean) * rstd, g[e], b[e]);
+      store8<T>(y + row * C + vi * 8, o8);
+    }
+  }
+}
+
+template <typename T, int LPR, int R>
+static cudaError_t ln_small_launch(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c, float eps,
+                                   cudaStream_t s) {
+  const long long per_warp = (32 / LPR) * R;
+  const long long warps = (rows + per_warp - 1) / per_warp;
+  const unsigned grid = (unsigned)((warps + 7) / 8);
+  return launch_pdl(layernorm_small_kernel<T, LPR, R>, dim3(grid), dim3(256), 0, s, reinterpret_cast<const T*>(x),
+                    reinterpret_cast<T*>(y), gamma, beta, rows, c, eps);
+}
+
 template <typename T, int NV, int R>
 static cudaError_t ln_launch(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c, float eps,
                              cudaStream_t s) {
@@ -101,6 +171,13 @@ cudaError_t launch_layernorm(const void* x, void* y, const float* gamma, const f
   if (c % 8 || c > 1024) return cudaErrorInvalidValue;
   const int nvl = (c / 8 + 31) / 32;   // 16-byte vectors per lane
   count_launch();
+  if (c <= 128) {      // several rows per warp
+    if (dtype == kBF16)
+      return c <= 64 ? ln_small_launch<bf16, 8, 4>(x, y, gamma, beta, rows, c, eps, s)
+                     : ln_small_launch<bf16, 16, 4>(x, y, gamma, beta, rows, c, eps, s);
+    return c <= 64 ? ln_small_launch<float, 8, 4>(x, y, gamma, beta, rows, c, eps, s)
+                   : ln_small_launch<float, 16, 4>(x, y, gamma, beta, rows, c, eps, s);
+  }
 #define LN_CASE(T_)                                                                         \
   if (nvl == 1) return ln_launch<T_, 1, 4>(x, y, gamma, beta, rows, c, eps, s);             \
   if (nvl == 2) return ln_launch<T_, 2, 2>(x, y, gamma, beta, rows, c, eps, s);             \

@@ -81,7 +81,7 @@ CONV_CASES = [
     (64, 64, 56, 1, ACT_NONE, True), (128, 128, 28, 1, ACT_GELU, False), (128, 128, 28, 1, ACT_NONE, True),
     (64, 128, 56, 2, ACT_NONE, False), (128, 256, 28, 2, ACT_NONE, False), (256, 512, 14, 2, ACT_NONE, False),
     (96, 96, 56, 1, ACT_GELU, False), (192, 384, 28, 2, ACT_NONE, False), (24, 40, 13, 1, ACT_GELU, True),
-    (8, 16, 9, 2, ACT_RELU, False),
+    (8, 16, 9, 2, ACT_RELU, False), (192, 192, 28, 1, ACT_NONE, True), (64, 64, 20, 1, ACT_GELU, True),
 ]
 
 
@@ -177,7 +177,7 @@ def test_attention(nseq, nq, nk, dk, dv, heads, th, vl, act, dt):
 
 
 @pytest.mark.parametrize("dt", [FP, BF])
-@pytest.mark.parametrize("rows,c,eps", [(1000, 256, 1e-5), (777, 512, 1e-5), (3136, 64, 1e-6), (50, 768, 1e-5), (33, 128, 1e-6)])
+@pytest.mark.parametrize("rows,c,eps", [(1000, 256, 1e-5), (777, 512, 1e-5), (3136, 64, 1e-6), (50, 768, 1e-5), (33, 128, 1e-6), (1001, 96, 1e-6), (67, 48, 1e-5), (5, 32, 1e-5)])
 def test_layernorm(rows, c, eps, dt):
     from gpu_util import k_layernorm, tdtype
 
