@@ -59,6 +59,43 @@ __device__ __forceinline__ f32x2_t c2_add(f32x2_t a, f32x2_t b) {
 
 struct TileCoord { int nt, tx, ty, g; };
 
+// Four K = 16 steps of one 64-wide K chunk in ONE asm block: the two descriptors differ from step to step only in the start
+// address (low word, +32 bytes = +2), so the issuing thread spends 3 instructions per MMA instead of the ~14 of the generic
+// 64-bit descriptor arithmetic.  With N <= 128 an MMA takes 32-64 clocks: the single issuing thread's instruction latency
+// -- not the tensor pipe, not L2 -- was what bounded the small-N kernels (ncu, profiles/r02_d_conv3x3.txt).  a_lo / b_lo: low words of
+// the K-major SW128 descriptors (make_sw128_kmajor_desc), hi: their common high word.  acc0: accumulate flag of step 0.
+__device__ __forceinline__ void umma_bf16_k4(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc,
+                                             uint32_t acc0) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p, t;\n"
+      ".reg .b32 a, b;\n"
+      ".reg .b64 da, db;\n"
+      "setp.ne.b32 p, %5, 0;\n"
+      "setp.eq.b32 t, 0, 0;\n"
+      "mov.b64 da, {%1, %3};\n"
+      "mov.b64 db, {%2, %3};\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n"
+      "add.u32 a, %1, 2;\n"
+      "add.u32 b, %2, 2;\n"
+      "mov.b64 da, {a, %3};\n"
+      "mov.b64 db, {b, %3};\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, t;\n"
+      "add.u32 a, %1, 4;\n"
+      "add.u32 b, %2, 4;\n"
+      "mov.b64 da, {a, %3};\n"
+      "mov.b64 db, {b, %3};\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, t;\n"
+      "add.u32 a, %1, 6;\n"
+      "add.u32 b, %2, 6;\n"
+      "mov.b64 da, {a, %3};\n"
+      "mov.b64 db, {b, %3};\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, t;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc0)
+      : "memory");
+}
+
 }  // namespace
 
 template <int kAct, bool kRes>
@@ -70,14 +107,20 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   const int b_bytes = p.bn * kCBK * 2;
   const int a_bytes = p.vhalo ? (p.th + 2) * 1024 : kCABytes;
   const int res_bytes = p.b_res ? p.k_chunks * b_bytes : 0;                       // resident weights in front of the ring
-  const int stage_bytes = a_bytes + (p.b_res ? 0 : (p.vhalo ? 3 : 1) * b_bytes);
+  // classic schedule: one ring of (A box + weight tile) stages.  vhalo: an A ring of 18-row boxes and, unless the weights are
+  // resident, a separate ring of weight tiles (three per A box) -- more, smaller stages in flight for the same shared memory
+  const int stage_bytes = p.vhalo ? a_bytes : a_bytes + (p.b_res ? 0 : b_bytes);
   uint8_t* ring = smem + res_bytes;
-  uint8_t* epi_smem = ring + (size_t)p.stages * stage_bytes;
-  float* sbias = reinterpret_cast<float*>(epi_smem + kCEpiWarps * kCEpiStageBytes);
+  uint8_t* bring = ring + (size_t)p.stages * stage_bytes;
+  uint8_t* epi_smem = bring + (size_t)p.b_stages * b_bytes;
+  const int epi_warps_alloc = p.bn > 64 ? kCEpiWarps : kCEpiWarps / 2;   // bn <= 64: the second column-half team never stores
+  float* sbias = reinterpret_cast<float*>(epi_smem + epi_warps_alloc * kCEpiStageBytes);
   uint64_t* bars = reinterpret_cast<uint64_t*>(sbias + kCMaxBias);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kCMaxStages;
-  uint64_t* tmem_full = bars + 2 * kCMaxStages;
+  uint64_t* bfull_bar = bars + 2 * kCMaxStages;
+  uint64_t* bempty_bar = bars + 3 * kCMaxStages;
+  uint64_t* tmem_full = bars + 4 * kCMaxStages;
   uint64_t* tmem_empty = tmem_full + 2;
   uint64_t* bres_bar = tmem_empty + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bres_bar + 1);
@@ -102,6 +145,10 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < p.b_stages; ++s) {
+      mbar_init(&bfull_bar[s], 1);
+      mbar_init(&bempty_bar[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
@@ -133,22 +180,29 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
       }
       __syncwarp();
     }
+    int sb = 0;
+    uint32_t phb = 0;
     for (int t = t_begin; p.vhalo && t < t_end; t += t_step) {
       const TileCoord tc_ = decode(t);
       const int ix0 = tc_.tx * 8 - 1, iy0 = tc_.ty * p.th - 1;
       for (int cc = 0; cc < p.cpt; ++cc)
         for (int kx = 0; kx < 3; ++kx) {
           mbar_wait(&empty_bar[s], ph ^ 1);
-          uint8_t* sa = ring + (size_t)s * stage_bytes;
           if (elect_one()) {
-            mbar_arrive_expect_tx(&full_bar[s], (uint32_t)stage_bytes);
-            tma_load_4d(sa, &tmap_x, cc * kCBK, ix0 + kx, iy0, tc_.g, &full_bar[s]);   // th + 2 rows: taps ky = 0, 1, 2
-            if (!p.b_res)
-              for (int ky = 0; ky < 3; ++ky)
-                tma_load_2d(sa + a_bytes + ky * b_bytes, &tmap_w, ((ky * 3 + kx) * p.cpt + cc) * kCBK, tc_.nt * p.bn, &full_bar[s]);
+            mbar_arrive_expect_tx(&full_bar[s], (uint32_t)a_bytes);
+            tma_load_4d(ring + (size_t)s * a_bytes, &tmap_x, cc * kCBK, ix0 + kx, iy0, tc_.g, &full_bar[s]);   // th + 2 rows: ky = 0, 1, 2
           }
           __syncwarp();
           if (++s == p.stages) { s = 0; ph ^= 1; }
+          for (int ky = 0; ky < 3 && !p.b_res; ++ky) {
+            mbar_wait(&bempty_bar[sb], phb ^ 1);
+            if (elect_one()) {
+              mbar_arrive_expect_tx(&bfull_bar[sb], (uint32_t)b_bytes);
+              tma_load_2d(bring + (size_t)sb * b_bytes, &tmap_w, ((ky * 3 + kx) * p.cpt + cc) * kCBK, tc_.nt * p.bn, &bfull_bar[sb]);
+            }
+            __syncwarp();
+            if (++sb == p.b_stages) { sb = 0; phb ^= 1; }
+          }
         }
     }
     for (int t = t_begin; !p.vhalo && t < t_end; t += t_step) {
@@ -173,7 +227,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     const uint32_t idesc = make_idesc_bf16_m128((uint32_t)p.bn);
     const uint64_t desc_res = make_sw128_kmajor_desc(smem_u32(smem));
     const uint64_t desc0 = make_sw128_kmajor_desc(smem_u32(ring));
+    const uint64_t desc_b0 = make_sw128_kmajor_desc(smem_u32(bring));
     const int stage16 = stage_bytes >> 4;
+    const uint32_t desc_hi = (uint32_t)(desc0 >> 32);
+    const uint32_t lo0 = (uint32_t)desc0, lo_res = (uint32_t)desc_res, lo_b0 = (uint32_t)desc_b0;
+    int sb = 0;
+    uint32_t phb = 0;
     int s = 0;
     uint32_t ph = 0;
     int lt = 0;
@@ -193,19 +252,35 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
         for (int kx = 0; kx < 3; ++kx) {
           mbar_wait(&full_bar[s], ph);
           tcgen05_fence_after();
-          const uint64_t da0 = desc0 + (uint64_t)(uint32_t)(s * stage16);
-          if (elect_one()) {
-            for (int ky = 0; ky < 3; ++ky) {
-              const uint64_t da = da0 + (uint64_t)(ky * (1024 >> 4));          // one image row of the tile = one swizzle atom
-              const uint64_t db = p.b_res ? desc_res + (uint64_t)(uint32_t)((((ky * 3 + kx) * p.cpt + cc) * b_bytes) >> 4)
-                                          : da0 + (uint64_t)(uint32_t)((a_bytes + ky * b_bytes) >> 4);
-              for (int k = 0; k < nk; ++k)
-                umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (cc | kx | ky | k) ? 1u : 0u);
+          const uint32_t a0 = lo0 + (uint32_t)(s * stage16);
+          for (int ky = 0; ky < 3; ++ky) {
+            const uint32_t a_lo = a0 + (uint32_t)(ky * (1024 >> 4));          // one image row of the tile = one swizzle atom
+            uint32_t b_lo;
+            if (p.b_res) {
+              b_lo = lo_res + (uint32_t)((((ky * 3 + kx) * p.cpt + cc) * b_bytes) >> 4);
+            } else {
+              mbar_wait(&bfull_bar[sb], phb);
+              tcgen05_fence_after();
+              b_lo = lo_b0 + (uint32_t)((sb * b_bytes) >> 4);
             }
-            umma_commit(&empty_bar[s]);
-            if (cc == p.cpt - 1 && kx == 2) umma_commit(&tmem_full[acc]);
+            if (elect_one()) {
+              const uint32_t first = (cc | kx | ky) ? 1u : 0u;
+              if (nk == 4) {
+                umma_bf16_k4(d_tmem, a_lo, b_lo, desc_hi, idesc, first);
+              } else {
+                for (int k = 0; k < nk; ++k)
+                  umma_bf16(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + 2 * k), ((uint64_t)desc_hi << 32) | (b_lo + 2 * k), idesc,
+                            (first | k) ? 1u : 0u);
+              }
+              if (!p.b_res) umma_commit(&bempty_bar[sb]);
+              if (ky == 2) {
+                umma_commit(&empty_bar[s]);
+                if (cc == p.cpt - 1 && kx == 2) umma_commit(&tmem_full[acc]);
+              }
+            }
+            __syncwarp();
+            if (!p.b_res && ++sb == p.b_stages) { sb = 0; phb ^= 1; }
           }
-          __syncwarp();
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
       }
@@ -225,8 +300,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
         const int crem = p.cin - cc * kCBK;                       // valid channels of this chunk
         const int nk = crem >= kCBK ? 4 : ((crem + 15) >> 4);     // K = 16 steps that hold any non-zero column
         if (elect_one()) {
-          for (int k = 0; k < nk; ++k)
-            umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kc | k) ? 1u : 0u);
+          if (nk == 4) {
+            umma_bf16_k4(d_tmem, (uint32_t)da, (uint32_t)db, desc_hi, idesc, kc ? 1u : 0u);
+          } else {
+            for (int k = 0; k < nk; ++k)
+              umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kc | k) ? 1u : 0u);
+          }
           umma_commit(&empty_bar[s]);
           if (kc == p.k_chunks - 1) umma_commit(&tmem_full[acc]);
         }
@@ -240,7 +319,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     const int grp = ew >> 3;          // accumulator this warp drains
     const int half = (ew >> 2) & 1;   // column-half team
     const int q = warp & 3;           // TMEM lane quarter = tile rows 32q .. 32q+31 = 4 image rows of 8 pixels
-    uint8_t* stg_base = epi_smem + ew * kCEpiStageBytes;
+    uint8_t* stg_base = epi_smem + (p.bn > 64 ? ew : grp * 4 + q) * kCEpiStageBytes;   // (bn <= 64: half-1 warps never store)
     const int img_in_tile = (4 * q) / p.th, y0 = (4 * q) % p.th;
     const int lx = lane & 7, ly = lane >> 3;
     int stores = 0, lt = 0;
@@ -338,10 +417,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 
 // ---- host side ---------------------------------------------------------------------------------------------------
 
-static size_t conv_tc_smem(int bn, int stages, size_t stage_bytes = 0, size_t res_bytes = 0) {
+static size_t conv_tc_smem(int bn, int stages, size_t stage_bytes = 0, size_t res_bytes = 0, int b_stages = 0) {
   if (!stage_bytes) stage_bytes = kCABytes + (size_t)bn * kCBK * 2;
-  return 1024 + res_bytes + (size_t)stages * stage_bytes + kCEpiWarps * kCEpiStageBytes + kCMaxBias * sizeof(float) +
-         (2 * kCMaxStages + 5) * sizeof(uint64_t) + 16;
+  const int epi_warps = bn > 64 ? kCEpiWarps : kCEpiWarps / 2;
+  return 1024 + res_bytes + (size_t)stages * stage_bytes + (size_t)b_stages * bn * kCBK * 2 + epi_warps * kCEpiStageBytes +
+         kCMaxBias * sizeof(float) + (4 * kCMaxStages + 5) * sizeof(uint64_t) + 16;
 }
 
 static bool conv_vhalo_enabled() {   // B200DF_CONV_VHALO=0: the one-box-per-tap schedule everywhere (A/B aid)
@@ -371,8 +451,14 @@ int plan_conv3x3_tc(Conv3Plan& plan, const void* x, int n, int h, int w, int cin
     const double eff = (double)Ho / ((Ho + th - 1) / th * th) * (double)n / ((n + ti - 1) / ti * ti);
     if (eff > best_eff + 1e-9) { best_eff = eff; best_th = th; }
   }
-  // stride 1: vertical-halo schedule (16-row tiles of ONE image; a few wasted rows at 56 / 28 buy 2.7x less A traffic)
-  p.vhalo = (stride == 1 && conv_vhalo_enabled()) ? 1 : 0;
+  // stride 1: vertical-halo schedule (16-row tiles of ONE image; a few wasted rows at 56 / 28 buy 2.7x less A traffic) when
+  // at least two of its stages (18 KB of A + three weight tiles, or A alone with resident weights) fit
+  p.vhalo = 0;
+  if (stride == 1 && conv_vhalo_enabled()) {
+    const size_t bb = (size_t)bn * kCBK * 2, kch = 9 * (size_t)(conv3x3_tc_cin_pad(cin) / kCBK);
+    const bool res_ok = cout_pad == bn && kch * bb <= 80 * 1024;
+    if (conv_tc_smem(bn, 3, 18 * 1024, res_ok ? kch * bb : 0, res_ok ? 0 : 3) <= 220 * 1024) p.vhalo = 1;
+  }
   if (p.vhalo) best_th = 16;
   p.cin = cin; p.cout = cout; p.cout_pad = cout_pad; p.bn = bn;
   p.Ho = Ho; p.Wo = Wo; p.stride = stride; p.n_img = n;
@@ -393,15 +479,22 @@ int plan_conv3x3_tc(Conv3Plan& plan, const void* x, int n, int h, int w, int cin
   const size_t b_bytes = (size_t)bn * kCBK * 2;
   p.b_res = (p.vhalo && p.n_tiles == 1 && p.k_chunks * b_bytes <= 80 * 1024) ? 1 : 0;
   const size_t res_bytes = p.b_res ? p.k_chunks * b_bytes : 0;
-  const size_t stage_bytes = p.vhalo ? (size_t)(p.th + 2) * 1024 + (p.b_res ? 0 : 3 * b_bytes) : kCABytes + b_bytes;
-  int stages = kCMaxStages;
-  while (stages > 2 && conv_tc_smem(bn, stages, stage_bytes, res_bytes) > 220 * 1024) --stages;
-  if (conv_tc_smem(bn, stages, stage_bytes, res_bytes) > 220 * 1024) return -1;
+  const size_t stage_bytes = p.vhalo ? (size_t)(p.th + 2) * 1024 : kCABytes + b_bytes;
+  int stages = kCMaxStages, b_stages = 0;
+  if (p.vhalo && !p.b_res) {   // three A boxes in flight, the rest of the budget for weight tiles (three per A box)
+    stages = 3;
+    b_stages = kCMaxStages;
+    while (b_stages > 3 && conv_tc_smem(bn, stages, stage_bytes, 0, b_stages) > 220 * 1024) --b_stages;
+  } else {
+    while (stages > 2 && conv_tc_smem(bn, stages, stage_bytes, res_bytes) > 220 * 1024) --stages;
+  }
+  if (conv_tc_smem(bn, stages, stage_bytes, res_bytes, b_stages) > 220 * 1024) return -1;
   p.stages = stages;
+  p.b_stages = b_stages;
   p.bias = bias;
   p.residual = reinterpret_cast<const bf16*>(residual);
   plan.act = act;
-  plan.smem = conv_tc_smem(bn, stages, stage_bytes, res_bytes);
+  plan.smem = conv_tc_smem(bn, stages, stage_bytes, res_bytes, b_stages);
   plan.grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
   // A: NHWC activations [cin, w, h, n], box [64, 8 s, th s, ti] traversed with stride s in W and H, 128B swizzle
   {

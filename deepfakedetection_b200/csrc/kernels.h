@@ -191,6 +191,7 @@ struct ConvTcParams {
   // vhalo (stride 1, th 16, ti 1): one A box of th + 2 rows serves the three taps of a kernel COLUMN (a row shift of the
   // 8-pixel-wide tile is one 1024-byte swizzle atom); b_res: all 9 * cpt weight tiles stay in shared memory (cout_pad == bn)
   int vhalo, b_res;
+  int b_stages;                   // vhalo without resident weights: the weight tiles have their own ring (stages = A ring)
   const float* bias;
   const __nv_bfloat16* residual;
 };
