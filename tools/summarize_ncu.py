@@ -12,6 +12,7 @@ from collections import OrderedDict
 def short(name: str) -> str:
     name = re.sub(r"^void\s+", "", name)
     name = name.replace("b200df::", "")
+    name = re.sub(r"(\(anonymous namespace\)|<?unnamed>)::", "", name)   # kernels in an unnamed namespace (attn_mma.cu, cam_bwd.cu)
     m = re.match(r"([\w:]+)(<[^>]*>)?", name)
     return (m.group(1) + (m.group(2) or "")) if m else name[:40]
 
