@@ -12,7 +12,8 @@
 //   attention_bwd      : dq, dk, dv of softmax(q k^T * scale + bias) v, one CTA per (sequence, head)
 //   conv3x3_s2_bwd     : backward-data of the level-2 downsample conv (3x3, stride 2, pad 1)
 //   move_rows          : backward of the carrier-token cat / split copies (the destination rows were overwritten)
-//   tail_bwd           : d logits[target] / d (level-3 output) of BatchNorm2d -> mean -> Linear
+//   tail_bwd           : d logits[target] / d (level-3 output) of BatchNorm2d -> mean -> Linear (general d loss / d logits
+//                        for the hook protocol: tail_bwd_general); ct_pool_bwd: the AvgPool2d's backward as fp32 NCHW
 //   cam_from_ct_grad   : channel weights = spatial mean of dA (through the AvgPool2d in closed form), cam = relu(sum_k w_k A_k)
 #include "common.cuh"
 #include "kernels.h"
@@ -111,6 +112,50 @@ tail_bwd_kernel(const float* __restrict__ n_scale, const float* __restrict__ w, 
   for (int i = threadIdx.x; i < HW * C; i += blockDim.x) {
     const int c = i % C;
     gn[i] = from_f<T>(ok ? __ldg(w + (size_t)cls * C + c) * __ldg(n_scale + c) * inv : __int_as_float(0x7fc00000));
+  }
+}
+
+// General form for the hook protocol (pytorch-grad-cam's loss.backward() with any d loss / d logits):
+// dA[p, c] = (sum_j gl[n, j] W[j, c]) * n_scale[c] / HW
+template <typename T>
+__global__ void __launch_bounds__(256)
+tail_bwd_general_kernel(const float* __restrict__ n_scale, const float* __restrict__ w, int HW, int C, int NC,
+                        const float* __restrict__ gl, T* __restrict__ g) {
+  extern __shared__ float wsum[];   // [C]
+  const int img = blockIdx.x;
+  const float inv = 1.0f / (float)HW;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s = 0.f;
+    for (int j = 0; j < NC; ++j) s = fmaf(gl[(size_t)img * NC + j], __ldg(w + (size_t)j * C + c), s);
+    wsum[c] = s * __ldg(n_scale + c) * inv;
+  }
+  __syncthreads();
+  T* gn = g + (size_t)img * HW * C;
+  for (int i = threadIdx.x; i < HW * C; i += blockDim.x) gn[i] = from_f<T>(wsum[i % C]);
+}
+
+// backward of the carrier-token initialiser's AvgPool2d(kernel, stride) (vit_ops.cu: ct_pool, windowed token order):
+// dA[n, c, y, x] = sum over pooled positions (py, px) whose window holds (y, x) of dct[n, tok(py, px), c] / kernel^2,
+// written as fp32 NCHW -- the tensor pytorch-grad-cam's gradient hook on the target layer receives.
+template <typename T>
+__global__ void __launch_bounds__(256)
+ct_pool_bwd_kernel(const T* __restrict__ gct, float* __restrict__ ga, int side, int C, int kernel, int stride, int g, int cs) {
+  const int img = blockIdx.y, nwin = g / cs;
+  const float inv = 1.0f / (float)(kernel * kernel);
+  const int total = C * side * side;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int x = i % side, y = (i / side) % side, c = i / (side * side);
+    float s = 0.f;
+    for (int py = 0; py < g; ++py) {
+      if (y < py * stride || y >= py * stride + kernel) continue;
+      for (int px = 0; px < g; ++px) {
+        if (x < px * stride || x >= px * stride + kernel) continue;
+        const int wy = py / cs, iy = py - wy * cs, wx = px / cs, ix = px - wx * cs;
+        const int tok = ((wy * nwin + wx) * cs + iy) * cs + ix;
+        s += to_f(gct[((size_t)img * g * g + tok) * C + c]);
+      }
+    }
+    ga[(size_t)img * total + i] = s * inv;
   }
 }
 
@@ -331,6 +376,30 @@ cudaError_t launch_tail_bwd(const float* n_scale, const float* w, int n, int hw,
   count_launch();
   if (dtype == kBF16) tail_bwd_kernel<bf16><<<n, 256, 0, s>>>(n_scale, w, hw, c, num_classes, target_cls, logits, mp<bf16>(g));
   else tail_bwd_kernel<float><<<n, 256, 0, s>>>(n_scale, w, hw, c, num_classes, target_cls, logits, mp<float>(g));
+  return cudaGetLastError();
+}
+
+cudaError_t launch_tail_bwd_general(const float* n_scale, const float* w, int n, int hw, int c, int num_classes,
+                                    const float* grad_logits, void* g, int dtype, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  if (c * sizeof(float) > 48 * 1024) return cudaErrorInvalidValue;
+  count_launch();
+  if (dtype == kBF16)
+    tail_bwd_general_kernel<bf16><<<n, 256, c * sizeof(float), s>>>(n_scale, w, hw, c, num_classes, grad_logits, mp<bf16>(g));
+  else
+    tail_bwd_general_kernel<float><<<n, 256, c * sizeof(float), s>>>(n_scale, w, hw, c, num_classes, grad_logits, mp<float>(g));
+  return cudaGetLastError();
+}
+
+cudaError_t launch_ct_pool_bwd(const void* gct, float* ga_nchw, int n, int side, int c, int kernel, int stride, int cs,
+                               int dtype, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  const int g = (side - kernel) / stride + 1;
+  if (g % cs) return cudaErrorInvalidValue;
+  const dim3 grid((c * side * side + 255) / 256, n);
+  count_launch();
+  if (dtype == kBF16) ct_pool_bwd_kernel<bf16><<<grid, 256, 0, s>>>(cp<bf16>(gct), ga_nchw, side, c, kernel, stride, g, cs);
+  else ct_pool_bwd_kernel<float><<<grid, 256, 0, s>>>(cp<float>(gct), ga_nchw, side, c, kernel, stride, g, cs);
   return cudaGetLastError();
 }
 

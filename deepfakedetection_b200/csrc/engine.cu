@@ -927,15 +927,28 @@ static int trunk_impl(b200df_handle h, const float* images, int n, float* a_nchw
   const int dt = h->precision == B200DF_PREC_BF16 ? kBF16 : kFP32;
   if (h->net) {
     Net* net = h->net.get();
-    if (!net->wcam) return fail(B200DF_E_STATE, "the split trunk/head (Grad-CAM hook) path is not built for this architecture");
+    const bool has_bwd = net->fwd_end >= 0 && (size_t)net->fwd_end < net->ops.size();
+    if (!net->wcam && !has_bwd)
+      return fail(B200DF_E_STATE, "the split trunk/head (Grad-CAM hook) path is not built for this architecture");
     if (!aux) return fail(B200DF_E_INVALID, "this architecture's split head needs the aux output (b200df_trunk_ex)");
     NetWs NW;
-    rc = check_net_call(h, n, workspace, workspace_bytes, &NW);
+    rc = check_net_call(h, n, workspace, workspace_bytes, &NW, net->wcam ? 0 : 1);
     if (rc) return rc;
+    const int fhw = net->feat_side * net->feat_side;
+    if (!net->wcam) {
+      // FasterViT: the whole forward with activation checkpoints; aux = the logits themselves (head_ex returns them,
+      // head_backward runs the backward program on the checkpoints this call leaves in `workspace`)
+      CamRun cr;
+      rc = run_net(h, images, kInF32NCHW, nullptr, nullptr, n, ws, NW, aux, s, 0, &cr);
+      if (rc) return rc;
+      CU_OK(launch_nhwc_to_nchw_f32(ws + NW.off[net->a_buf], n, fhw, net->feat_c, a_nchw, dt, s));
+      h->cam_ws = workspace;
+      h->cam_n = n;
+      return B200DF_OK;
+    }
     float* lg = reinterpret_cast<float*>(ws + NW.logits);
     rc = run_net(h, images, kInF32NCHW, nullptr, nullptr, n, ws, NW, lg, s);
     if (rc) return rc;
-    const int fhw = net->feat_side * net->feat_side;
     CU_OK(launch_nhwc_to_nchw_f32(ws + NW.off[net->a_buf], n, fhw, net->feat_c, a_nchw, dt, s));
     CU_OK(launch_lin_head(a_nchw, lg, n, fhw, net->feat_c, net->wcam, h->num_classes, 1, aux, s));
     return B200DF_OK;
@@ -980,8 +993,15 @@ static int head_impl(b200df_handle h, const float* a_nchw, const float* aux, int
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (h->net) {
     Net* net = h->net.get();
-    if (!net->wcam) return fail(B200DF_E_STATE, "the split trunk/head (Grad-CAM hook) path is not built for this architecture");
+    const bool has_bwd = net->fwd_end >= 0 && (size_t)net->fwd_end < net->ops.size();
+    if (!net->wcam && !has_bwd)
+      return fail(B200DF_E_STATE, "the split trunk/head (Grad-CAM hook) path is not built for this architecture");
     if (!aux) return fail(B200DF_E_INVALID, "this architecture's split head needs the aux input (b200df_head_ex)");
+    if (!net->wcam) {   // FasterViT: aux holds the logits of the trunk call (the path from A to them is not a function of A alone)
+      if (logits != aux)
+        CU_OK(cudaMemcpyAsync(logits, aux, (size_t)n * h->num_classes * sizeof(float), cudaMemcpyDeviceToDevice, s));
+      return B200DF_OK;
+    }
     CU_OK(launch_lin_head(a_nchw, aux, n, net->feat_side * net->feat_side, net->feat_c, net->wcam, h->num_classes, 0, logits, s));
     return B200DF_OK;
   }
@@ -1054,7 +1074,21 @@ extern "C" int b200df_head_backward(b200df_handle h, const float* a_nchw, const 
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (h->net) {
     Net* net = h->net.get();
-    if (!net->wcam) return fail(B200DF_E_STATE, "the split trunk/head (Grad-CAM hook) path is not built for this architecture");
+    const bool has_bwd = net->fwd_end >= 0 && (size_t)net->fwd_end < net->ops.size();
+    if (!net->wcam && !has_bwd)
+      return fail(B200DF_E_STATE, "the split trunk/head (Grad-CAM hook) path is not built for this architecture");
+    if (!net->wcam) {
+      // FasterViT: the backward program on the checkpoints of the LAST b200df_trunk_ex call of this engine (its workspace
+      // must still be alive and untouched; same batch size)
+      if (!h->cam_ws || h->cam_n != n)
+        return fail(B200DF_E_STATE, "b200df_head_backward: no matching b200df_trunk_ex call (batch %d, last trunk batch %d)", n,
+                    h->cam_n);
+      const NetWs NW = layout_net_workspace(h, n, 1);
+      CamRun cr;
+      cr.grad_logits = grad_logits;
+      cr.grad_a = grad_a_nchw;
+      return run_net(h, nullptr, kInF32NCHW, nullptr, nullptr, n, reinterpret_cast<uint8_t*>(h->cam_ws), NW, nullptr, s, 1, &cr);
+    }
     CU_OK(launch_lin_head_backward(grad_logits, n, net->feat_side * net->feat_side, net->feat_c, net->wcam, h->num_classes,
                                    grad_a_nchw, s));
     return B200DF_OK;

@@ -139,6 +139,10 @@ struct b200df_engine {
   std::vector<b200df::Plan> plans;   // a few (n, workspace) plans, least recently used evicted
   unsigned long long plan_clock = 0;
   std::unique_ptr<b200df::Net> net;  // layer program (EfficientFormerV2 / FasterViT); null for the MBConv engines
+  // hook protocol on a layer program with a backward program (FasterViT): b200df_trunk_ex leaves the activation checkpoints
+  // in its workspace; b200df_head_backward runs the backward program on them
+  void* cam_ws = nullptr;
+  int cam_n = 0;
   float* head_scratch = nullptr;     // pooled [n, head_c] for the split (hook-protocol) head, grown outside captures
   size_t head_scratch_cap = 0;
   // profiling (off by default; never on inside a timed region)

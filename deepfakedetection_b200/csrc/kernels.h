@@ -263,6 +263,10 @@ cudaError_t launch_move_rows(void* src, void* dst, long long nseq, int src_rows,
                              int nrows, int c, int dtype, cudaStream_t s);
 cudaError_t launch_tail_bwd(const float* n_scale, const float* w, int n, int hw, int c, int num_classes,
                             const int32_t* target_cls, const float* logits, void* g, int dtype, cudaStream_t s);
+cudaError_t launch_tail_bwd_general(const float* n_scale, const float* w, int n, int hw, int c, int num_classes,
+                                    const float* grad_logits, void* g, int dtype, cudaStream_t s);
+cudaError_t launch_ct_pool_bwd(const void* gct, float* ga_nchw, int n, int side, int c, int kernel, int stride, int cs,
+                               int dtype, cudaStream_t s);
 cudaError_t launch_cam_from_ct_grad(const void* a, const void* gct, int n, int hw, int c, int ntok, float* cam_lowres,
                                     int dtype, cudaStream_t s);
 cudaError_t launch_conv3x3_s2_bwd(const void* dy, const void* w, void* dx, int n, int hin, int cin, int cinp, int cout,

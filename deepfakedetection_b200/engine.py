@@ -223,7 +223,9 @@ class Engine:
         if n == 0:
             return a, aux
         with self._lock, torch.cuda.device(images.device):
-            base, size = self._workspace(n)
+            # mode 1: on FasterViT the trunk leaves the activation checkpoints of the Grad-CAM backward program in this
+            # workspace; head_backward runs on them (the workspace stays cached per (n, stream) until evicted)
+            base, size = self._workspace(n, mode=1)
             _lib.check(self._lib.b200df_trunk_ex(self._h, _ptr(images), n, _ptr(a), _ptr(aux), C.c_void_p(base), size,
                                                 _stream_ptr(images.device)))
         return a, aux

@@ -210,10 +210,8 @@ class B200Module(nn.Module):
             # backward (inference engine): gradients stop at A, which is all Grad-CAM needs.
             if not self.supports_cam_hooks:
                 raise NotImplementedError(
-                    f"b200 {self.arch_name}: the reference's Grad-CAM target rule (web_ui.py:96-105) picks a conv in front of "
-                    "this network's transformer blocks; the backward pass through them exists only inside the fused "
-                    "forward_cam() / deepfakedetection_b200.gradcam.GradCAM(use_hooks=False) path, not as an autograd graph.  "
-                    "Call the model under torch.inference_mode()/no_grad().")
+                    f"b200 {self.arch_name}: no autograd path to the Grad-CAM target of this backbone.  "
+                    "Call the model under torch.inference_mode()/no_grad(), or use forward_cam().")
             a, aux = ops.trunk(images.detach(), self._engine_id)
             a = self._cam_point()(a.requires_grad_(True))
             return ops.head(a, aux, self._engine_id)

@@ -11,8 +11,8 @@ names and shapes so that the reference's ``load
 (orchestrator.py:370-375) fills them; no arithmetic ever runs in PyTorch.  Module registration ORDER follows the
 packages too, because the reference picks its Grad-CAM target as "the last nn.Conv2d in modules() order"
 (/root/reference/web_ui.py:96-105): that is ``stages.3.blocks.5.mlp.fc2.conv`` for EfficientFormerV2-S1 (served: the
-map after it is affine, closed form) and ``levels.2.global_tokenizer.pos_embed`` for FasterViT (not served: needs a
-backward pass through 11 transformer blocks).
+map after it is affine, closed form) and ``levels.2.global_tokenizer.pos_embed`` for FasterViT (served by the engine's
+backward pass through the transformer blocks behind it, csrc/cam_bwd.cu).
 """
 
 from __future__ import annotations
@@ -299,12 +299,13 @@ _FV_CFG = {
 class B200FasterViT(B200Module):
     """Drop-in for ``fastervit.create_model("faster_vit_0_224" | "faster_vit_2_224")`` + ``head = nn.Linear(...)``.
 
-    Grad-CAM: the reference's target rule (web_ui.py:94-112) picks ``levels.2.global_tokenizer.pos_embed``; the fused
-    ``forward_cam`` runs the engine's backward program through every block behind it (csrc/cam_bwd.cu).  The map is
-    14x14 before the upsample.  The hook protocol (forward with grad enabled) is not offered: there is no autograd graph."""
+    Grad-CAM: the reference's target rule (web_ui.py:94-112) picks ``levels.2.global_tokenizer.pos_embed``; the engine's
+    backward program runs through every block behind it (csrc/cam_bwd.cu), in the fused ``forward_cam`` and -- for the
+    real pytorch-grad-cam package -- behind the hook protocol: a forward with grad enabled returns logits whose autograd
+    edge to the (14 x 14) target activation is that backward program."""
 
     supports_cam = True
-    supports_cam_hooks = False
+    supports_cam_hooks = True
 
     def __init__(self, num_classes: int = 2, precision: str = "bf16", variant: str = "faster_vit_0_224") -> None:
         if variant not in _FV_CFG:

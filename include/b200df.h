@@ -132,8 +132,11 @@ int b200df_head_backward(b200df_handle h, const float* a_nchw, const float* grad
 /* Same split with an auxiliary per-image term, aux float32 [n,num_classes]: EfficientFormerV2's Grad-CAM target
  * (the last nn.Conv2d, `stages.3.blocks.5.mlp.fc2.conv`, web_ui.py:96-105) is followed by an AFFINE map whose offset
  * depends on the block's residual input, not on A: trunk_ex writes aux = logits - lin(A), head_ex(A, aux) = aux + lin(A).
- * The EfficientNet engines write / ignore zeros.  FasterViT has no split path (B200DF_E_STATE): its Grad-CAM is
- * served by b200df_forward_cam only. */
+ * The EfficientNet engines write / ignore zeros.  FasterViT (target in front of the transformer blocks): trunk_ex runs the
+ * whole forward with activation checkpoints, A = the pos_embed conv's output [n,C,14,14], aux = the logits; head_ex
+ * returns aux; b200df_head_backward runs the backward program (csrc/cam_bwd.cu) from grad_logits on the checkpoints the
+ * LAST trunk_ex call of this engine left in its workspace -- keep that workspace alive and untouched in between; another
+ * batch size is refused with B200DF_E_STATE. */
 int b200df_trunk_ex(b200df_handle h, const float* images, int n, float* a_nchw, float* aux, void* workspace,
                     size_t workspace_bytes, void* stream);
 int b200df_head_ex(b200df_handle h, const float* a_nchw, const float* aux, int n, float* logits, void* stream);

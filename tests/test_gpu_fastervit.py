@@ -115,10 +115,9 @@ def test_bf16_simt_paths_agree_with_tcgen05(monkeypatch):
     assert (a - b).pow(2).mean().sqrt().item() <= 0.05 * ref.std().item()
 
 
-def test_gradcam_target_is_the_reference_rule_and_hooks_are_refused():
-    """The reference's target rule picks `levels.2.global_tokenizer.pos_embed` (web_ui.py:94-112).  The backward pass through
-    the 11 transformer blocks behind it exists inside the fused forward_cam only: a forward with grad enabled (the hook
-    protocol) must say so, not return a graph-less tensor."""
+def test_gradcam_target_is_the_reference_rule():
+    """The reference's target rule picks `levels.2.global_tokenizer.pos_embed` (web_ui.py:94-112) on the backend module
+    exactly as on the fastervit package's module tree."""
     from oracle.fastervit import make_seeded_oracle
 
     ref_model = make_seeded_oracle(seed=0)
@@ -129,9 +128,47 @@ def test_gradcam_target_is_the_reference_rule_and_hooks_are_refused():
             last = name
     assert last == ref_model.cam_target()[0] == "levels.2.global_tokenizer.pos_embed"
     assert model._cam_point() is model.levels[2].global_tokenizer.pos_embed
-    with pytest.raises(NotImplementedError):
-        with torch.enable_grad():
-            model(torch.zeros(1, 3, 224, 224, device="cuda"))
+
+
+@pytest.mark.parametrize("prec", [".b200_fp32", ""])
+def test_gradcam_hook_protocol_through_the_transformer_blocks(calibrated, prec):
+    """pytorch-grad-cam's own mechanism (forward hook on the target layer, tensor hook on its output, loss.backward()):
+    a forward with grad enabled returns logits whose autograd edge to the target activation is the engine's backward
+    program.  The activation and its gradient are compared with the oracle's; the map with the fused path's."""
+    from deepfakedetection_b200.gradcam import ClassifierOutputTarget, GradCAM
+    from oracle.gradcam import gradcam_on_layer
+
+    name, m, x, ref = calibrated
+    n = 3
+    tgt = ref[:n].argmax(1)
+    tgt[0] = 1 - tgt[0]
+    _, _, cam_ref, a_ref, g_ref = gradcam_on_layer(m, m.cam_target()[1], x[:n], tgt)
+    model = build(m, name + prec)
+    store = {}
+    hd = model._cam_point().register_forward_hook(
+        lambda _m, _i, out: (store.__setitem__("A", out), out.register_hook(lambda g: store.__setitem__("G", g)))[0] and None)
+    with torch.enable_grad():
+        logits = model(x[:n].cuda())
+        logits[torch.arange(n), tgt.cuda()].sum().backward()
+    hd.remove()
+    a, g = store["A"].detach().cpu(), store["G"].cpu()
+    assert a.shape == g.shape == a_ref.shape == (n, a_ref.shape[1], 14, 14)
+    if prec:
+        torch.testing.assert_close(a, a_ref, atol=2e-4 * a_ref.abs().max().item(), rtol=1e-3)
+        assert (g - g_ref).abs().max().item() <= 2e-3 * g_ref.abs().max().item()
+    w, w_ref = g.mean((2, 3)), g_ref.mean((2, 3))
+    cosw = torch.nn.functional.cosine_similarity(w, w_ref, dim=1).min().item()
+    assert cosw >= 0.99, f"channel weights cosine {cosw}"
+    # the packaged front end in hook mode == the fused path
+    with GradCAM(model=model, target_layers=[model._cam_point()], use_hooks=True) as cam:
+        gray = cam(input_tensor=x[:n].cuda(), targets=[ClassifierOutputTarget(int(c)) for c in tgt])
+    _, _, fused = model.forward_cam(x[:n].cuda(), tgt)
+    keep = cam_ref.flatten(1).max(1).values > 0
+    cos = torch.nn.functional.cosine_similarity(torch.as_tensor(gray).flatten(1), fused.cpu().flatten(1), dim=1)[keep].min().item()
+    assert cos >= 0.999, f"hooked vs fused cosine {cos}"
+    # a backward without a matching forward is refused, not answered from stale checkpoints
+    with pytest.raises(Exception):
+        model._engine.head_backward(torch.zeros(n + 1, a.shape[1], 14, 14, device="cuda"), torch.zeros(n + 1, 2, device="cuda"))
 
 
 @pytest.mark.parametrize("prec", [".b200_fp32", ""])
