@@ -39,10 +39,14 @@ def _scale(cam: torch.Tensor) -> torch.Tensor:
 
 
 class GradCAM:
-    def __init__(self, model, target_layers, reshape_transform=None, use_hooks: bool = False) -> None:
+    def __init__(self, model, target_layers, reshape_transform=None, use_hooks: bool | None = None) -> None:
         self.model = model.eval()
         self.target_layers = list(target_layers)
         self.reshape_transform = reshape_transform
+        if use_hooks is None:   # B200DF_GRADCAM_HOOKS=1: pytorch-grad-cam's own mechanism (hooks + backward) instead of the fused call
+            import os
+
+            use_hooks = os.environ.get("B200DF_GRADCAM_HOOKS", "0") not in ("", "0")
         self.use_hooks = use_hooks
         self.outputs: torch.Tensor | None = None
 

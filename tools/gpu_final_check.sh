@@ -12,6 +12,8 @@ python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/f_ref.json 2>
 tail -3 gpurun_out/f.err
 if [ -d .refcopy ]; then
   python tools/run_reference_on_backend.py --reference-root $PWD/.refcopy --ui --images 16 > gpurun_out/f_reference_on_backend.txt 2>&1; tail -14 gpurun_out/f_reference_on_backend.txt
+  # the same web_ui run with Grad-CAM through hooks + loss.backward() (pytorch-grad-cam's mechanism) instead of the fused call
+  B200DF_GRADCAM_HOOKS=1 python tools/run_reference_on_backend.py --reference-root $PWD/.refcopy --ui --images 8 --models efficientnet_b3,efficientformerv2_s1,faster_vit_2_224,faster_vit_0_224 > gpurun_out/f_reference_on_backend_hooks.txt 2>&1; tail -8 gpurun_out/f_reference_on_backend_hooks.txt
 fi
 python tools/ncu_step.py 256 x efficientformerv2_s1 > gpurun_out/f_plain_efv2.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/f_launches_efv2.csv python tools/ncu_step.py 256 x efficientformerv2_s1 > gpurun_out/f_ncu_efv2.log 2>&1
 tail -1 gpurun_out/f_ncu_efv2.log
