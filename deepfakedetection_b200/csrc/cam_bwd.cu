@@ -238,95 +238,206 @@ conv3x3_s2_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ w, T* __re
 // ---- attention backward -------------------------------------------------------------------------------------------------------
 // Forward (attn.cu / attn_mma.cu, no talking heads): S = q k^T * scale + bias, P = softmax_j(S), o = P v.
 // Given do:  dv = P^T do;  dP = do v^T;  dS = P * (dP - rowsum(dP * P));  dq = scale * dS k;  dk = scale * dS^T q.
-// One CTA per (sequence, head); q, k, v, do of the head and the two score matrices live in shared memory in fp32.
+// One CTA per (sequence, head); everything of the head lives in shared memory in fp32.  The five small products run on
+// 4 x 4 register tiles per thread -- the first version (one output per thread, two shared-memory loads per FMA) was
+// bound by the shared-memory pipe: 155 us per launch.  K and V are also kept TRANSPOSED ([d][key], keys padded to a
+// multiple of 4 with zeros) so that four consecutive keys are one 16-byte load.
+__host__ __device__ inline int abw_r4(int x) { return (x + 3) & ~3; }
+// float offsets of the shared-memory arrays
+struct AbwLayout {
+  int qp, vp, kp, sp;            // pitches: q / k rows (dk + 4), do rows (dv + 4), transposed rows / score rows (keys4 + 4)
+  int qs, ks, kT, vT, os, P, D, total;
+  __host__ __device__ AbwLayout(int nq, int nk, int dk, int dv) {
+    qp = dk + 4; vp = dv + 4; kp = abw_r4(nk) + 4; sp = kp;
+    qs = 0;
+    ks = qs + nq * qp;
+    kT = ks + nk * qp;
+    vT = kT + dk * kp;
+    os = vT + dv * kp;
+    P = os + nq * vp;
+    D = P + nq * sp;
+    total = D + nq * sp;
+  }
+};
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 attention_bwd_kernel(const AttnArgs a, const T* __restrict__ dout, T* __restrict__ dq, T* __restrict__ dk, T* __restrict__ dv) {
-  extern __shared__ float sm[];
+  extern __shared__ __align__(16) float sm[];
   const int seq = blockIdx.x, h = blockIdx.y;
   const int nq = a.nq, nk = a.nk, dkk = a.dk, dvv = a.dv, H = a.heads;
-  const int sp = nk + 1, qp = dkk + 1, vp = dvv + 1;
-  float* qs = sm;                  // [nq][dk + 1]
-  float* ks = qs + nq * qp;        // [nk][dk + 1]
-  float* vs = ks + nk * qp;        // [nk][dv + 1]
-  float* os = vs + nk * vp;        // [nq][dv + 1]   do
-  float* P = os + nq * vp;         // [nq][nk + 1]
-  float* D = P + nq * sp;          // [nq][nk + 1]   dP, then dS
+  const AbwLayout L(nq, nk, dkk, dvv);
+  float* qs = sm + L.qs;   // [nq][qp]
+  float* ks = sm + L.ks;   // [nk][qp]
+  float* kT = sm + L.kT;   // [dk][kp]   keys >= nk: 0
+  float* vT = sm + L.vT;   // [dv][kp]
+  float* os = sm + L.os;   // [nq][vp]   do
+  float* P = sm + L.P;     // [nq][sp]
+  float* D = sm + L.D;     // [nq][sp]   dP, then dS
   const T* q = reinterpret_cast<const T*>(a.q);
   const T* k = reinterpret_cast<const T*>(a.k);
   const T* v = reinterpret_cast<const T*>(a.v);
   const int tid = threadIdx.x, nt = blockDim.x;
-  const int oc = H * dvv;
+  const int oc = H * dvv, nk4 = abw_r4(nk) >> 2, nq4 = abw_r4(nq) >> 2;
+  for (int i = tid; i < (dkk + dvv) * L.kp; i += nt) kT[i] = 0.f;   // kT and vT are adjacent: zero incl. the key padding
+  __syncthreads();
   for (int i = tid; i < nq * dkk; i += nt) {
     const int r = i / dkk, d = i - r * dkk;
-    qs[r * qp + d] = to_f(q[((size_t)seq * nq + r) * a.q_pitch + a.q_off + h * dkk + d]);
+    qs[r * L.qp + d] = to_f(q[((size_t)seq * nq + r) * a.q_pitch + a.q_off + h * dkk + d]);
   }
   for (int i = tid; i < nk * dkk; i += nt) {
     const int r = i / dkk, d = i - r * dkk;
-    ks[r * qp + d] = to_f(k[((size_t)seq * nk + r) * a.k_pitch + a.k_off + h * dkk + d]);
+    const float x = to_f(k[((size_t)seq * nk + r) * a.k_pitch + a.k_off + h * dkk + d]);
+    ks[r * L.qp + d] = x;
+    kT[d * L.kp + r] = x;
   }
   for (int i = tid; i < nk * dvv; i += nt) {
     const int r = i / dvv, d = i - r * dvv;
-    vs[r * vp + d] = to_f(v[((size_t)seq * nk + r) * a.v_pitch + a.v_off + h * dvv + d]);
+    vT[d * L.kp + r] = to_f(v[((size_t)seq * nk + r) * a.v_pitch + a.v_off + h * dvv + d]);
   }
   for (int i = tid; i < nq * dvv; i += nt) {
     const int r = i / dvv, d = i - r * dvv;
-    os[r * vp + d] = to_f(dout[((size_t)seq * nq + r) * oc + h * dvv + d]);
+    os[r * L.vp + d] = to_f(dout[((size_t)seq * nq + r) * oc + h * dvv + d]);
   }
   __syncthreads();
-  for (int idx = tid; idx < nq * nk; idx += nt) {
-    const int i = idx / nk, j = idx - i * nk;
-    float s = 0.f, dp = 0.f;
-    for (int e = 0; e < dkk; ++e) s = fmaf(qs[i * qp + e], ks[j * qp + e], s);
-    for (int e = 0; e < dvv; ++e) dp = fmaf(os[i * vp + e], vs[j * vp + e], dp);
-    s *= a.scale;
-    if (a.bias) s += __ldg(a.bias + ((size_t)h * nq + i) * nk + j);
-    P[i * sp + j] = s;
-    D[i * sp + j] = dp;
+  // S = scale q k^T + bias and dP = do v^T on 4 (queries) x 4 (keys) tiles
+  for (int item = tid; item < nq4 * nk4; item += nt) {
+    const int i0 = (item / nk4) * 4, j0 = (item - (item / nk4) * nk4) * 4;
+    int ir[4];
+#pragma unroll
+    for (int ii = 0; ii < 4; ++ii) ir[ii] = min(i0 + ii, nq - 1);
+    float sacc[4][4], pacc[4][4];
+#pragma unroll
+    for (int ii = 0; ii < 4; ++ii)
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) sacc[ii][jj] = pacc[ii][jj] = 0.f;
+    for (int e = 0; e < dkk; ++e) {
+      const float4 kk = *reinterpret_cast<const float4*>(kT + e * L.kp + j0);
+#pragma unroll
+      for (int ii = 0; ii < 4; ++ii) {
+        const float qv = qs[ir[ii] * L.qp + e];
+        sacc[ii][0] = fmaf(qv, kk.x, sacc[ii][0]); sacc[ii][1] = fmaf(qv, kk.y, sacc[ii][1]);
+        sacc[ii][2] = fmaf(qv, kk.z, sacc[ii][2]); sacc[ii][3] = fmaf(qv, kk.w, sacc[ii][3]);
+      }
+    }
+    for (int e = 0; e < dvv; ++e) {
+      const float4 vv = *reinterpret_cast<const float4*>(vT + e * L.kp + j0);
+#pragma unroll
+      for (int ii = 0; ii < 4; ++ii) {
+        const float ov = os[ir[ii] * L.vp + e];
+        pacc[ii][0] = fmaf(ov, vv.x, pacc[ii][0]); pacc[ii][1] = fmaf(ov, vv.y, pacc[ii][1]);
+        pacc[ii][2] = fmaf(ov, vv.z, pacc[ii][2]); pacc[ii][3] = fmaf(ov, vv.w, pacc[ii][3]);
+      }
+    }
+#pragma unroll
+    for (int ii = 0; ii < 4; ++ii) {
+      const int i = i0 + ii;
+      if (i >= nq) continue;
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        const int jx = j0 + jj;
+        float sv = -INFINITY;   // key padding: P = 0
+        if (jx < nk) {
+          sv = sacc[ii][jj] * a.scale;
+          if (a.bias) sv += __ldg(a.bias + ((size_t)h * nq + i) * nk + jx);
+        }
+        P[i * L.sp + jx] = sv;
+        D[i * L.sp + jx] = jx < nk ? pacc[ii][jj] : 0.f;
+      }
+    }
   }
   __syncthreads();
-  {   // softmax rows, then dS = P * (dP - sum_j dP P): one warp per row
-    const int lane = tid & 31, warp = tid >> 5;
+  {   // softmax rows, then dS = P * (dP - sum_j dP P): one warp per row (padded keys: P = exp(-inf) = 0)
+    const int lane = tid & 31, warp = tid >> 5, nkp = nk4 * 4;
     for (int i = warp; i < nq; i += nt >> 5) {
-      float* pr = P + i * sp;
-      float* dr = D + i * sp;
+      float* pr = P + i * L.sp;
+      float* dr = D + i * L.sp;
       float mx = -INFINITY;
-      for (int j = lane; j < nk; j += 32) mx = fmaxf(mx, pr[j]);
+      for (int jx = lane; jx < nkp; jx += 32) mx = fmaxf(mx, pr[jx]);
       mx = warp_max(mx);
       float sum = 0.f;
-      for (int j = lane; j < nk; j += 32) {
-        const float e = expf(pr[j] - mx);
-        pr[j] = e;
+      for (int jx = lane; jx < nkp; jx += 32) {
+        const float e = expf(pr[jx] - mx);
+        pr[jx] = e;
         sum += e;
       }
       const float inv = 1.0f / warp_sum(sum);
       float dot = 0.f;
-      for (int j = lane; j < nk; j += 32) {
-        pr[j] *= inv;
-        dot = fmaf(dr[j], pr[j], dot);
+      for (int jx = lane; jx < nkp; jx += 32) {
+        pr[jx] *= inv;
+        dot = fmaf(dr[jx], pr[jx], dot);
       }
       dot = warp_sum(dot);
-      for (int j = lane; j < nk; j += 32) dr[j] = pr[j] * (dr[j] - dot);
+      for (int jx = lane; jx < nkp; jx += 32) dr[jx] = pr[jx] * (dr[jx] - dot);
     }
   }
   __syncthreads();
-  for (int idx = tid; idx < nk * dvv; idx += nt) {   // dv[j, d] = sum_i P[i, j] do[i, d]
-    const int j = idx / dvv, d = idx - j * dvv;
-    float s = 0.f;
-    for (int i = 0; i < nq; ++i) s = fmaf(P[i * sp + j], os[i * vp + d], s);
-    dv[((size_t)seq * nk + j) * a.v_pitch + a.v_off + h * dvv + d] = from_f<T>(s);
+  // dv[j, d] = sum_i P[i, j] do[i, d]  and  dk[j, d] = scale sum_i dS[i, j] q[i, d]  on 4 (keys) x 4 (channels) tiles
+  {
+    const int dv4 = dvv >> 2, dk4 = dkk >> 2;
+    for (int item = tid; item < nk4 * (dv4 + dk4); item += nt) {
+      const int j0 = (item / (dv4 + dk4)) * 4, c = item - (item / (dv4 + dk4)) * (dv4 + dk4);
+      const bool is_v = c < dv4;
+      const int d0 = (is_v ? c : c - dv4) * 4;
+      const float* lhs = is_v ? P : D;                       // [i][j]
+      const float* rhs = is_v ? os + d0 : qs + d0;           // [i][d]
+      const int rp = is_v ? L.vp : L.qp;
+      float acc[4][4];
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+        for (int dd = 0; dd < 4; ++dd) acc[jj][dd] = 0.f;
+      for (int i = 0; i < nq; ++i) {
+        const float4 l4 = *reinterpret_cast<const float4*>(lhs + i * L.sp + j0);
+        const float4 r4 = *reinterpret_cast<const float4*>(rhs + i * rp);
+        const float lv[4] = {l4.x, l4.y, l4.z, l4.w};
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          acc[jj][0] = fmaf(lv[jj], r4.x, acc[jj][0]); acc[jj][1] = fmaf(lv[jj], r4.y, acc[jj][1]);
+          acc[jj][2] = fmaf(lv[jj], r4.z, acc[jj][2]); acc[jj][3] = fmaf(lv[jj], r4.w, acc[jj][3]);
+        }
+      }
+      const float sc = is_v ? 1.0f : a.scale;
+      T* dst = is_v ? dv : dk;
+      const int pitch = is_v ? a.v_pitch : a.k_pitch, off = is_v ? a.v_off + h * dvv : a.k_off + h * dkk;
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        if (j0 + jj >= nk) continue;
+#pragma unroll
+        for (int dd = 0; dd < 4; ++dd) dst[((size_t)seq * nk + j0 + jj) * pitch + off + d0 + dd] = from_f<T>(acc[jj][dd] * sc);
+      }
+    }
   }
-  for (int idx = tid; idx < nq * dkk; idx += nt) {   // dq[i, d] = scale * sum_j dS[i, j] k[j, d]
-    const int i = idx / dkk, d = idx - i * dkk;
-    float s = 0.f;
-    for (int j = 0; j < nk; ++j) s = fmaf(D[i * sp + j], ks[j * qp + d], s);
-    dq[((size_t)seq * nq + i) * a.q_pitch + a.q_off + h * dkk + d] = from_f<T>(s * a.scale);
-  }
-  for (int idx = tid; idx < nk * dkk; idx += nt) {   // dk[j, d] = scale * sum_i dS[i, j] q[i, d]
-    const int j = idx / dkk, d = idx - j * dkk;
-    float s = 0.f;
-    for (int i = 0; i < nq; ++i) s = fmaf(D[i * sp + j], qs[i * qp + d], s);
-    dk[((size_t)seq * nk + j) * a.k_pitch + a.k_off + h * dkk + d] = from_f<T>(s * a.scale);
+  // dq[i, d] = scale sum_j dS[i, j] k[j, d]  on 4 (queries) x 4 (channels) tiles
+  {
+    const int dk4 = dkk >> 2;
+    for (int item = tid; item < nq4 * dk4; item += nt) {
+      const int i0 = (item / dk4) * 4, d0 = (item - (item / dk4) * dk4) * 4;
+      int ir[4];
+#pragma unroll
+      for (int ii = 0; ii < 4; ++ii) ir[ii] = min(i0 + ii, nq - 1);
+      float acc[4][4];
+#pragma unroll
+      for (int ii = 0; ii < 4; ++ii)
+#pragma unroll
+        for (int dd = 0; dd < 4; ++dd) acc[ii][dd] = 0.f;
+      for (int jx = 0; jx < nk; ++jx) {
+        const float4 k4 = *reinterpret_cast<const float4*>(ks + jx * L.qp + d0);
+#pragma unroll
+        for (int ii = 0; ii < 4; ++ii) {
+          const float dsv = D[ir[ii] * L.sp + jx];
+          acc[ii][0] = fmaf(dsv, k4.x, acc[ii][0]); acc[ii][1] = fmaf(dsv, k4.y, acc[ii][1]);
+          acc[ii][2] = fmaf(dsv, k4.z, acc[ii][2]); acc[ii][3] = fmaf(dsv, k4.w, acc[ii][3]);
+        }
+      }
+#pragma unroll
+      for (int ii = 0; ii < 4; ++ii) {
+        if (i0 + ii >= nq) continue;
+#pragma unroll
+        for (int dd = 0; dd < 4; ++dd)
+          dq[((size_t)seq * nq + i0 + ii) * a.q_pitch + a.q_off + h * dkk + d0 + dd] = from_f<T>(acc[ii][dd] * a.scale);
+      }
+    }
   }
 }
 
@@ -433,8 +544,8 @@ cudaError_t launch_conv3x3_s2_bwd(const void* dy, const void* w, void* dx, int n
 cudaError_t launch_attention_bwd(const AttnArgs& a, const void* dout, void* dq, void* dk, void* dv, int dtype, cudaStream_t s) {
   if (a.nseq <= 0) return cudaSuccess;
   if (a.th1_w || a.vlocal || a.act != kActNone) return cudaErrorNotSupported;
-  const size_t smem = ((size_t)(a.nq + a.nk) * (a.dk + 1) + (size_t)(a.nq + a.nk) * (a.dv + 1) + 2 * (size_t)a.nq * (a.nk + 1)) *
-                      sizeof(float);
+  if (a.dk % 4 || a.dv % 4) return cudaErrorInvalidValue;
+  const size_t smem = (size_t)AbwLayout(a.nq, a.nk, a.dk, a.dv).total * sizeof(float);
   if (smem > 200 * 1024) return cudaErrorInvalidValue;
   static PerDeviceOnce once_b, once_f;
   count_launch();
