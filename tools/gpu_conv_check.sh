@@ -1,3 +1,4 @@
+# A/B of the dense 3x3 conv schedules + the kernels that changed with them (profiles/r02_d_conv3x3.txt): B200DF_CONV_VHALO=0 is the one-box-per-tap schedule
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_gpu_vit_kernels.py -x -q -m gpu -k "conv3x3 or layernorm or upsample" > gpurun_out/t_conv.log 2>&1; tail -6 gpurun_out/t_conv.log
 timeout 900 python -m pytest tests/test_gpu_fastervit.py tests/test_gpu_efv2.py -x -q -m gpu > gpurun_out/t_conv2.log 2>&1; tail -4 gpurun_out/t_conv2.log
