@@ -10,6 +10,8 @@ python bench.py --model faster_vit_2_224 --no-e2e --no-cpu-baseline > gpurun_out
 python bench.py --model efficientnet_b3 --no-e2e --no-cpu-baseline > gpurun_out/f_b3.json 2>> gpurun_out/f.err
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/f_ref.json 2>> gpurun_out/f.err
 tail -3 gpurun_out/f.err
+# the reference checkout does not exist on the GPU box: for this one evidence run a temporary, git-ignored copy of it
+# (`cp -r /root/reference .refcopy`, deleted again afterwards) travels with the snapshot; nothing in the product reads it
 if [ -d .refcopy ]; then
   python tools/run_reference_on_backend.py --reference-root $PWD/.refcopy --ui --images 16 > gpurun_out/f_reference_on_backend.txt 2>&1; tail -14 gpurun_out/f_reference_on_backend.txt
   # the same web_ui run with Grad-CAM through hooks + loss.backward() (pytorch-grad-cam's mechanism) instead of the fused call
