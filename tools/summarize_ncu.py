@@ -68,6 +68,11 @@ def step(path: str) -> None:
     # the tensor-pipe column: whichever sm__pipe_tensor* / sm__inst_executed_pipe_tensor* percentage this ncu version exports
     tens = [h for h in hdr if "pipe_tensor" in h and "pct_of_peak" in h]
     tens = [h for h in tens if "cycles_active" in h] or tens
+    # tcgen05.mma runs on the `tc` pipe: sm__pipe_tensor* (the mma.sync / HMMA pipe) reads 1-15 % on kernels whose
+    # sm__pipe_tc_cycles_active is 40-60 % -- prefer the tc pipe when this ncu version exports it
+    tc = [h for h in hdr if h.startswith("sm__pipe_tc_cycles_active.avg.pct_of_peak_sustained_elapsed")]
+    if tc:
+        tens = tc
     if tens:
         cols = [(tens[0], c[1], c[2]) if c[1] == "tens%" else c for c in cols]
     print("# one forward step (N=256, bf16), ncu --set full --clock-control none; dram bytes are per launch"
