@@ -80,6 +80,11 @@ SIGNATURES: dict[str, tuple] = {
     "b200df_k_attention": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp,
                                 _vp, _i, _vp, _i, _vp]),
     "b200df_k_layernorm": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _f, _i, _vp]),
+    "b200df_k_attention_bwd": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp, _vp, _i, _vp]),
+    "b200df_k_layernorm_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _i, _vp]),
+    "b200df_k_gelu_bwd": (_i, [_vp, _vp, _ll, _i, _vp]),
+    "b200df_k_conv3x3_s2_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "b200df_k_ct_pool_bwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "b200df_k_upsample2x_act": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
 }
 

@@ -1383,6 +1383,44 @@ extern "C" int b200df_k_layernorm(const void* x, void* y, const float* gamma, co
   return B200DF_OK;
 }
 
+// ---- backward-data kernels of the FasterViT Grad-CAM program (cam_bwd.cu), exposed for direct tests ----
+extern "C" int b200df_k_attention_bwd(const void* qkv, int pitch, int q_off, int k_off, int v_off, int nseq, int n_tok, int d,
+                                      int heads, float scale, const float* bias, const void* dout, void* dqkv, int dtype,
+                                      void* stream) {
+  AttnArgs a;
+  memset(&a, 0, sizeof(a));
+  a.q = a.k = a.v = qkv;
+  a.q_pitch = a.k_pitch = a.v_pitch = pitch;
+  a.q_off = q_off; a.k_off = k_off; a.v_off = v_off;
+  a.nseq = nseq; a.nq = a.nk = n_tok; a.dk = a.dv = d; a.heads = heads; a.scale = scale; a.bias = bias;
+  CU_OK(launch_attention_bwd(a, dout, dqkv, dqkv, dqkv, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_layernorm_bwd(const void* x, const float* gamma, const void* dy, const void* res, void* out,
+                                      long long rows, int c, float eps, int dtype, void* stream) {
+  CU_OK(launch_layernorm_bwd(x, gamma, dy, res, out, rows, c, eps, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_gelu_bwd(const void* pre, void* g, long long total, int dtype, void* stream) {
+  CU_OK(launch_gelu_bwd(pre, g, total, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+// wgt: [cout, 9, cin] in `dtype` (tap-major, the layout the forward kernels read with cin_pad == cin)
+extern "C" int b200df_k_conv3x3_s2_bwd(const void* dy, const void* wgt, void* dx, int n, int hin, int cin, int cout, int dtype,
+                                       void* stream) {
+  CU_OK(launch_conv3x3_s2_bwd(dy, wgt, dx, n, hin, cin, cin, cout, dtype, S(stream)));
+  return B200DF_OK;
+}
+
+extern "C" int b200df_k_ct_pool_bwd(const void* gct, float* ga_nchw, int n, int side, int c, int kernel, int stride, int cs,
+                                    int dtype, void* stream) {
+  CU_OK(launch_ct_pool_bwd(gct, ga_nchw, n, side, c, kernel, stride, cs, dtype, S(stream)));
+  return B200DF_OK;
+}
+
 extern "C" int b200df_k_upsample2x_act(const void* x, void* y, int n, int side, int c, int act, int dtype, void* stream) {
   CU_OK(launch_upsample2x_act(x, y, n, side, c, act, dtype, S(stream)));
   return B200DF_OK;

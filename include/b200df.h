@@ -289,6 +289,23 @@ int b200df_k_attention(const void* q, const void* k, const void* v, int q_pitch,
 int b200df_k_layernorm(const void* x, void* y, const float* gamma, const float* beta, long long rows, int c, float eps,
                        int dtype, void* stream);
 
+/* Backward-DATA kernels of the FasterViT Grad-CAM program (csrc/cam_bwd.cu; pytorch-grad-cam's loss.backward() through the
+ * blocks behind the target layer, web_ui.py:275-279).  Tensors in `dtype`, fp32 math.
+ *   attention_bwd : qkv / dqkv [nseq * n_tok, pitch] fused q|k|v rows (head h at off + h*d); dout [nseq * n_tok, heads*d]
+ *   layernorm_bwd : out = res + dLayerNorm(x; gamma)(dy)   (res may be NULL)
+ *   gelu_bwd      : g *= gelu'(pre), erf form, in place
+ *   conv3x3_s2_bwd: dx [n,hin,hin,cin] of a 3x3 stride-2 pad-1 conv given dy [n,hin/2,hin/2,cout], wgt [cout, 9, cin]
+ *   ct_pool_bwd   : fp32 NCHW gradient of the carrier-token AvgPool2d(kernel, stride) given dct [n, g*g, c] (windowed order) */
+int b200df_k_attention_bwd(const void* qkv, int pitch, int q_off, int k_off, int v_off, int nseq, int n_tok, int d, int heads,
+                           float scale, const float* bias, const void* dout, void* dqkv, int dtype, void* stream);
+int b200df_k_layernorm_bwd(const void* x, const float* gamma, const void* dy, const void* res, void* out, long long rows,
+                           int c, float eps, int dtype, void* stream);
+int b200df_k_gelu_bwd(const void* pre, void* g, long long total, int dtype, void* stream);
+int b200df_k_conv3x3_s2_bwd(const void* dy, const void* wgt, void* dx, int n, int hin, int cin, int cout, int dtype,
+                            void* stream);
+int b200df_k_ct_pool_bwd(const void* gct, float* ga_nchw, int n, int side, int c, int kernel, int stride, int cs, int dtype,
+                         void* stream);
+
 /* nn.Upsample(scale_factor=2, mode="bilinear") + act on NHWC [n,side,side,c] -> [n,2 side,2 side,c]. */
 int b200df_k_upsample2x_act(const void* x, void* y, int n, int side, int c, int act, int dtype, void* stream);
 
