@@ -24,52 +24,99 @@ namespace {
 
 // ---- LayerNorm backward ------------------------------------------------------------------------------------------
 // y = (x - mean) * rstd * gamma + beta  ->  dx = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma
-// out = res + dx (res nullable).  One warp per row, three passes over a row that stays in L1.
+// out = res + dx (res nullable).  One warp per row.
+// C % 8 == 0, C <= 1024: a lane keeps its (up to four) 16-byte vectors of x and dy in registers across the passes.
 template <typename T>
 __global__ void __launch_bounds__(256)
 layernorm_bwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma, const T* __restrict__ dy,
                      const T* __restrict__ res, T* __restrict__ out, long long rows, int C, float eps) {
+  griddep_wait();
+  griddep_launch_dependents();
   const int lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
-  const T* xr = x + row * C;
-  const T* dr = dy + row * C;
+  const int nv = C >> 3;
+  float xv[4][8], gv[4][8];
   float sum = 0.f;
-  for (int c = lane; c < C; c += 32) sum += to_f(xr[c]);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int vi = lane + 32 * i;
+    if (vi < nv) {
+      float d8[8], g8[8];
+      load8<T>(x + row * C + vi * 8, xv[i]);
+      load8<T>(dy + row * C + vi * 8, d8);
+      load8<float>(gamma + vi * 8, g8);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        gv[i][e] = d8[e] * g8[e];
+        sum += xv[i][e];
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) xv[i][e] = gv[i][e] = 0.f;
+    }
+  }
   const float mean = warp_sum(sum) / (float)C;
   float sq = 0.f;
-  for (int c = lane; c < C; c += 32) {
-    const float d = to_f(xr[c]) - mean;
-    sq = fmaf(d, d, sq);
-  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (lane + 32 * i < nv) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float d = xv[i][e] - mean;
+        sq = fmaf(d, d, sq);
+      }
+    }
   const float rstd = 1.0f / sqrtf(warp_sum(sq) / (float)C + eps);
   float sg = 0.f, sgx = 0.f;
-  for (int c = lane; c < C; c += 32) {
-    const float g = to_f(dr[c]) * __ldg(gamma + c);
-    sg += g;
-    sgx = fmaf(g, (to_f(xr[c]) - mean) * rstd, sgx);
-  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (lane + 32 * i < nv) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        xv[i][e] = (xv[i][e] - mean) * rstd;     // xhat
+        sg += gv[i][e];
+        sgx = fmaf(gv[i][e], xv[i][e], sgx);
+      }
+    }
   sg = warp_sum(sg) / (float)C;
   sgx = warp_sum(sgx) / (float)C;
-  for (int c = lane; c < C; c += 32) {
-    const float g = to_f(dr[c]) * __ldg(gamma + c);
-    const float xh = (to_f(xr[c]) - mean) * rstd;
-    float d = rstd * (g - sg - xh * sgx);
-    if (res) d += to_f(res[row * C + c]);
-    out[row * C + c] = from_f<T>(d);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int vi = lane + 32 * i;
+    if (vi < nv) {
+      float o[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = rstd * (gv[i][e] - sg - xv[i][e] * sgx);
+      if (res) {
+        float r8[8];
+        load8<T>(res + row * C + vi * 8, r8);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] += r8[e];
+      }
+      store8<T>(out + row * C + vi * 8, o);
+    }
   }
 }
 
-// ---- GELU backward (erf form: Phi(x) + x * phi(x)) ---------------------------------------------------------------------
+// ---- GELU backward (erf form: Phi(x) + x * phi(x)), eight elements per thread -------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256)
-gelu_bwd_kernel(const T* __restrict__ pre, T* __restrict__ g, long long total) {
+gelu_bwd_kernel(const T* __restrict__ pre, T* __restrict__ g, long long total8) {
+  griddep_wait();
+  griddep_launch_dependents();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= total) return;
-  const float x = to_f(pre[i]);
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.3989422804014327f * expf(-0.5f * x * x);
-  g[i] = from_f<T>(to_f(g[i]) * fmaf(x, pdf, cdf));
+  if (i >= total8) return;
+  float x[8], d[8];
+  load8<T>(pre + i * 8, x);
+  load8<T>(g + i * 8, d);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const float cdf = 0.5f * (1.0f + erff(x[e] * 0.70710678118654752f));
+    const float pdf = 0.3989422804014327f * expf(-0.5f * x[e] * x[e]);
+    d[e] *= fmaf(x[e], pdf, cdf);
+  }
+  store8<T>(g + i * 8, d);
 }
 
 // ---- move rows: dst[seq, dst_off + r, :] = src[seq, src_off + r, :]; src rows <- 0 -----------------------------------------
@@ -77,6 +124,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 move_rows_kernel(T* __restrict__ src, T* __restrict__ dst, long long nseq, int src_rows, int src_off, int dst_rows,
                  int dst_off, int nrows, int C) {
+  griddep_wait();
+  griddep_launch_dependents();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long total = nseq * nrows * C;
   if (i >= total) return;
@@ -94,6 +143,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 tail_bwd_kernel(const float* __restrict__ n_scale, const float* __restrict__ w, int HW, int C, int NC,
                 const int32_t* __restrict__ target_cls, const float* __restrict__ logits, T* __restrict__ g) {
+  griddep_wait();
+  griddep_launch_dependents();
   const int img = blockIdx.x;
   int cls;
   if (target_cls) {
@@ -121,6 +172,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 tail_bwd_general_kernel(const float* __restrict__ n_scale, const float* __restrict__ w, int HW, int C, int NC,
                         const float* __restrict__ gl, T* __restrict__ g) {
+  griddep_wait();
+  griddep_launch_dependents();
   extern __shared__ float wsum[];   // [C]
   const int img = blockIdx.x;
   const float inv = 1.0f / (float)HW;
@@ -140,6 +193,8 @@ tail_bwd_general_kernel(const float* __restrict__ n_scale, const float* __restri
 template <typename T>
 __global__ void __launch_bounds__(256)
 ct_pool_bwd_kernel(const T* __restrict__ gct, float* __restrict__ ga, int side, int C, int kernel, int stride, int g, int cs) {
+  griddep_wait();
+  griddep_launch_dependents();
   const int img = blockIdx.y, nwin = g / cs;
   const float inv = 1.0f / (float)(kernel * kernel);
   const int total = C * side * side;
@@ -166,6 +221,8 @@ ct_pool_bwd_kernel(const T* __restrict__ gct, float* __restrict__ ga, int side, 
 template <typename T>
 __global__ void __launch_bounds__(256)
 cam_from_ct_grad_kernel(const T* __restrict__ a, const T* __restrict__ gct, int HW, int C, int NT, float* __restrict__ cam) {
+  griddep_wait();
+  griddep_launch_dependents();
   extern __shared__ float wch[];   // [C]
   const int img = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const T* gn = gct + (size_t)img * NT * C;
@@ -193,6 +250,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 conv3x3_s2_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ w, T* __restrict__ dx, int n, int hin, int cin, int cinp,
                       int cout) {
+  griddep_wait();
+  griddep_launch_dependents();
   extern __shared__ float sdy[];   // [kCbImgs][cout]
   const int ho = (hin - 1) / 2 + 1;
   const int ix = blockIdx.x % hin, iy = blockIdx.x / hin;
@@ -263,6 +322,8 @@ struct AbwLayout {
 template <typename T>
 __global__ void __launch_bounds__(256)
 attention_bwd_kernel(const AttnArgs a, const T* __restrict__ dout, T* __restrict__ dq, T* __restrict__ dk, T* __restrict__ dv) {
+  griddep_wait();
+  griddep_launch_dependents();
   extern __shared__ __align__(16) float sm[];
   const int seq = blockIdx.x, h = blockIdx.y;
   const int nq = a.nq, nk = a.nk, dkk = a.dk, dvv = a.dv, H = a.heads;
@@ -443,29 +504,34 @@ attention_bwd_kernel(const AttnArgs a, const T* __restrict__ dout, T* __restrict
 
 }  // namespace
 
-// ---- launchers (plain stream-ordered launches: none of these kernels reads its inputs before its predecessor is done) ------
+// ---- launchers (programmatic dependent launch like the forward kernels: every kernel starts with griddepcontrol.wait) ------
 template <typename T> static const T* cp(const void* p) { return reinterpret_cast<const T*>(p); }
 template <typename T> static T* mp(void* p) { return reinterpret_cast<T*>(p); }
 
 cudaError_t launch_layernorm_bwd(const void* x, const float* gamma, const void* dy, const void* res, void* out,
                                  long long rows, int c, float eps, int dtype, cudaStream_t s) {
   if (rows <= 0) return cudaSuccess;
+  if (c % 8 || c > 1024) return cudaErrorInvalidValue;
   const unsigned grid = (unsigned)((rows + 7) / 8);
   count_launch();
+  cudaError_t e_ = cudaSuccess;
   if (dtype == kBF16)
-    layernorm_bwd_kernel<bf16><<<grid, 256, 0, s>>>(cp<bf16>(x), gamma, cp<bf16>(dy), cp<bf16>(res), mp<bf16>(out), rows, c, eps);
+    e_ = launch_pdl(layernorm_bwd_kernel<bf16>, dim3(grid), dim3(256), 0, s, cp<bf16>(x), gamma, cp<bf16>(dy), cp<bf16>(res), mp<bf16>(out), rows, c, eps);
   else
-    layernorm_bwd_kernel<float><<<grid, 256, 0, s>>>(cp<float>(x), gamma, cp<float>(dy), cp<float>(res), mp<float>(out), rows, c, eps);
-  return cudaGetLastError();
+    e_ = launch_pdl(layernorm_bwd_kernel<float>, dim3(grid), dim3(256), 0, s, cp<float>(x), gamma, cp<float>(dy), cp<float>(res), mp<float>(out), rows, c, eps);
+  return e_;
 }
 
 cudaError_t launch_gelu_bwd(const void* pre, void* g, long long total, int dtype, cudaStream_t s) {
   if (total <= 0) return cudaSuccess;
-  const unsigned grid = (unsigned)((total + 255) / 256);
+  if (total % 8) return cudaErrorInvalidValue;
+  const long long total8 = total / 8;
+  const unsigned grid = (unsigned)((total8 + 255) / 256);
   count_launch();
-  if (dtype == kBF16) gelu_bwd_kernel<bf16><<<grid, 256, 0, s>>>(cp<bf16>(pre), mp<bf16>(g), total);
-  else gelu_bwd_kernel<float><<<grid, 256, 0, s>>>(cp<float>(pre), mp<float>(g), total);
-  return cudaGetLastError();
+  cudaError_t e_ = cudaSuccess;
+  if (dtype == kBF16) e_ = launch_pdl(gelu_bwd_kernel<bf16>, dim3(grid), dim3(256), 0, s, cp<bf16>(pre), mp<bf16>(g), total8);
+  else e_ = launch_pdl(gelu_bwd_kernel<float>, dim3(grid), dim3(256), 0, s, cp<float>(pre), mp<float>(g), total8);
+  return e_;
 }
 
 cudaError_t launch_move_rows(void* src, void* dst, long long nseq, int src_rows, int src_off, int dst_rows, int dst_off,
@@ -474,20 +540,22 @@ cudaError_t launch_move_rows(void* src, void* dst, long long nseq, int src_rows,
   if (total <= 0) return cudaSuccess;
   const unsigned grid = (unsigned)((total + 255) / 256);
   count_launch();
+  cudaError_t e_ = cudaSuccess;
   if (dtype == kBF16)
-    move_rows_kernel<bf16><<<grid, 256, 0, s>>>(mp<bf16>(src), mp<bf16>(dst), nseq, src_rows, src_off, dst_rows, dst_off, nrows, c);
+    e_ = launch_pdl(move_rows_kernel<bf16>, dim3(grid), dim3(256), 0, s, mp<bf16>(src), mp<bf16>(dst), nseq, src_rows, src_off, dst_rows, dst_off, nrows, c);
   else
-    move_rows_kernel<float><<<grid, 256, 0, s>>>(mp<float>(src), mp<float>(dst), nseq, src_rows, src_off, dst_rows, dst_off, nrows, c);
-  return cudaGetLastError();
+    e_ = launch_pdl(move_rows_kernel<float>, dim3(grid), dim3(256), 0, s, mp<float>(src), mp<float>(dst), nseq, src_rows, src_off, dst_rows, dst_off, nrows, c);
+  return e_;
 }
 
 cudaError_t launch_tail_bwd(const float* n_scale, const float* w, int n, int hw, int c, int num_classes,
                             const int32_t* target_cls, const float* logits, void* g, int dtype, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   count_launch();
-  if (dtype == kBF16) tail_bwd_kernel<bf16><<<n, 256, 0, s>>>(n_scale, w, hw, c, num_classes, target_cls, logits, mp<bf16>(g));
-  else tail_bwd_kernel<float><<<n, 256, 0, s>>>(n_scale, w, hw, c, num_classes, target_cls, logits, mp<float>(g));
-  return cudaGetLastError();
+  cudaError_t e_ = cudaSuccess;
+  if (dtype == kBF16) e_ = launch_pdl(tail_bwd_kernel<bf16>, dim3(n), dim3(256), 0, s, n_scale, w, hw, c, num_classes, target_cls, logits, mp<bf16>(g));
+  else e_ = launch_pdl(tail_bwd_kernel<float>, dim3(n), dim3(256), 0, s, n_scale, w, hw, c, num_classes, target_cls, logits, mp<float>(g));
+  return e_;
 }
 
 cudaError_t launch_tail_bwd_general(const float* n_scale, const float* w, int n, int hw, int c, int num_classes,
@@ -495,11 +563,12 @@ cudaError_t launch_tail_bwd_general(const float* n_scale, const float* w, int n,
   if (n <= 0) return cudaSuccess;
   if (c * sizeof(float) > 48 * 1024) return cudaErrorInvalidValue;
   count_launch();
+  cudaError_t e_ = cudaSuccess;
   if (dtype == kBF16)
-    tail_bwd_general_kernel<bf16><<<n, 256, c * sizeof(float), s>>>(n_scale, w, hw, c, num_classes, grad_logits, mp<bf16>(g));
+    e_ = launch_pdl(tail_bwd_general_kernel<bf16>, dim3(n), dim3(256), c * sizeof(float), s, n_scale, w, hw, c, num_classes, grad_logits, mp<bf16>(g));
   else
-    tail_bwd_general_kernel<float><<<n, 256, c * sizeof(float), s>>>(n_scale, w, hw, c, num_classes, grad_logits, mp<float>(g));
-  return cudaGetLastError();
+    e_ = launch_pdl(tail_bwd_general_kernel<float>, dim3(n), dim3(256), c * sizeof(float), s, n_scale, w, hw, c, num_classes, grad_logits, mp<float>(g));
+  return e_;
 }
 
 cudaError_t launch_ct_pool_bwd(const void* gct, float* ga_nchw, int n, int side, int c, int kernel, int stride, int cs,
@@ -509,9 +578,10 @@ cudaError_t launch_ct_pool_bwd(const void* gct, float* ga_nchw, int n, int side,
   if (g % cs) return cudaErrorInvalidValue;
   const dim3 grid((c * side * side + 255) / 256, n);
   count_launch();
-  if (dtype == kBF16) ct_pool_bwd_kernel<bf16><<<grid, 256, 0, s>>>(cp<bf16>(gct), ga_nchw, side, c, kernel, stride, g, cs);
-  else ct_pool_bwd_kernel<float><<<grid, 256, 0, s>>>(cp<float>(gct), ga_nchw, side, c, kernel, stride, g, cs);
-  return cudaGetLastError();
+  cudaError_t e_ = cudaSuccess;
+  if (dtype == kBF16) e_ = launch_pdl(ct_pool_bwd_kernel<bf16>, dim3(grid), dim3(256), 0, s, cp<bf16>(gct), ga_nchw, side, c, kernel, stride, g, cs);
+  else e_ = launch_pdl(ct_pool_bwd_kernel<float>, dim3(grid), dim3(256), 0, s, cp<float>(gct), ga_nchw, side, c, kernel, stride, g, cs);
+  return e_;
 }
 
 cudaError_t launch_cam_from_ct_grad(const void* a, const void* gct, int n, int hw, int c, int ntok, float* cam_lowres,
@@ -519,11 +589,12 @@ cudaError_t launch_cam_from_ct_grad(const void* a, const void* gct, int n, int h
   if (n <= 0) return cudaSuccess;
   if (c * sizeof(float) > 48 * 1024) return cudaErrorInvalidValue;
   count_launch();
+  cudaError_t e_ = cudaSuccess;
   if (dtype == kBF16)
-    cam_from_ct_grad_kernel<bf16><<<n, 256, c * sizeof(float), s>>>(cp<bf16>(a), cp<bf16>(gct), hw, c, ntok, cam_lowres);
+    e_ = launch_pdl(cam_from_ct_grad_kernel<bf16>, dim3(n), dim3(256), c * sizeof(float), s, cp<bf16>(a), cp<bf16>(gct), hw, c, ntok, cam_lowres);
   else
-    cam_from_ct_grad_kernel<float><<<n, 256, c * sizeof(float), s>>>(cp<float>(a), cp<float>(gct), hw, c, ntok, cam_lowres);
-  return cudaGetLastError();
+    e_ = launch_pdl(cam_from_ct_grad_kernel<float>, dim3(n), dim3(256), c * sizeof(float), s, cp<float>(a), cp<float>(gct), hw, c, ntok, cam_lowres);
+  return e_;
 }
 
 cudaError_t launch_conv3x3_s2_bwd(const void* dy, const void* w, void* dx, int n, int hin, int cin, int cinp, int cout,
@@ -533,11 +604,12 @@ cudaError_t launch_conv3x3_s2_bwd(const void* dy, const void* w, void* dx, int n
   const dim3 grid(hin * hin, (n + kCbImgs - 1) / kCbImgs);
   const size_t smem = (size_t)kCbImgs * cout * sizeof(float);
   count_launch();
+  cudaError_t e_ = cudaSuccess;
   if (dtype == kBF16)
-    conv3x3_s2_bwd_kernel<bf16><<<grid, 256, smem, s>>>(cp<bf16>(dy), cp<bf16>(w), mp<bf16>(dx), n, hin, cin, cinp, cout);
+    e_ = launch_pdl(conv3x3_s2_bwd_kernel<bf16>, dim3(grid), dim3(256), smem, s, cp<bf16>(dy), cp<bf16>(w), mp<bf16>(dx), n, hin, cin, cinp, cout);
   else
-    conv3x3_s2_bwd_kernel<float><<<grid, 256, smem, s>>>(cp<float>(dy), cp<float>(w), mp<float>(dx), n, hin, cin, cinp, cout);
-  return cudaGetLastError();
+    e_ = launch_pdl(conv3x3_s2_bwd_kernel<float>, dim3(grid), dim3(256), smem, s, cp<float>(dy), cp<float>(w), mp<float>(dx), n, hin, cin, cinp, cout);
+  return e_;
 }
 
 // dq / dk / dv are written with q's / k's / v's pitch and column offset (the fused q|k|v layout of the forward GEMM).
@@ -549,21 +621,22 @@ cudaError_t launch_attention_bwd(const AttnArgs& a, const void* dout, void* dq, 
   if (smem > 200 * 1024) return cudaErrorInvalidValue;
   static PerDeviceOnce once_b, once_f;
   count_launch();
+  cudaError_t e_ = cudaSuccess;
   const dim3 grid(a.nseq, a.heads);
   if (dtype == kBF16) {
     if (once_b.need()) {
       cudaError_t e = cudaFuncSetAttribute(attention_bwd_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
       if (e != cudaSuccess) return e;
     }
-    attention_bwd_kernel<bf16><<<grid, 256, smem, s>>>(a, cp<bf16>(dout), mp<bf16>(dq), mp<bf16>(dk), mp<bf16>(dv));
+    e_ = launch_pdl(attention_bwd_kernel<bf16>, dim3(grid), dim3(256), smem, s, a, cp<bf16>(dout), mp<bf16>(dq), mp<bf16>(dk), mp<bf16>(dv));
   } else {
     if (once_f.need()) {
       cudaError_t e = cudaFuncSetAttribute(attention_bwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
       if (e != cudaSuccess) return e;
     }
-    attention_bwd_kernel<float><<<grid, 256, smem, s>>>(a, cp<float>(dout), mp<float>(dq), mp<float>(dk), mp<float>(dv));
+    e_ = launch_pdl(attention_bwd_kernel<float>, dim3(grid), dim3(256), smem, s, a, cp<float>(dout), mp<float>(dq), mp<float>(dk), mp<float>(dv));
   }
-  return cudaGetLastError();
+  return e_;
 }
 
 }  // namespace b200df

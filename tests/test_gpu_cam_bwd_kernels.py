@@ -85,8 +85,8 @@ def test_layernorm_bwd(rows, c, res, dt):
 @pytest.mark.parametrize("dt", [FP, BF])
 def test_gelu_bwd(dt):
     g = gen(3)
-    pre = (torch.randn(5000, device="cuda", generator=g) * 2).to(tdt(dt))
-    dh = torch.randn(5000, device="cuda", generator=g).to(tdt(dt))
+    pre = (torch.randn(5000 * 8, device="cuda", generator=g) * 2).to(tdt(dt))
+    dh = torch.randn(5000 * 8, device="cuda", generator=g).to(tdt(dt))
     xf = pre.float().requires_grad_(True)
     F.gelu(xf).backward(dh.float())
     got = dh.clone()
