@@ -518,6 +518,8 @@ def run_extras(args, model, images, labels, dev, rank, world, local, sync_all, s
     ms = timed_steps(lambda: model.forward_cam(x64, None), 50, dev, world, local)
     cam = {"metric": "efficientnet_b0_gradcam_maps_per_s", "value": round(world * 64 * 50 / (ms * 1e-3), 1), "unit": "maps/s",
            "batch_per_gpu": 64, "ms_per_step": round(ms / 50, 4), "config": "BASELINE.json configs[2]: forward + fused Grad-CAM, batch 64"}
+    # the UI's regime (web_ui.py:241-306): one image, forward + Grad-CAM
+    cam["latency_n1_ms"] = round(timed_steps(lambda: model.forward_cam(x1, None), 100, dev, 1, local) / 100, 4)
     tab = class_table(model._engine, lambda: model.forward_cam(x64, None), dev)
     cam["kernels"] = {c: {k2: v[k2] for k2 in ("ms", "launches", "GBps")} for c, v in tab.items() if c in ("cam", "cam_upsample", "conv_head", "dw")}
     out["cam"] = cam
@@ -556,6 +558,7 @@ def run_extras(args, model, images, labels, dev, rank, world, local, sync_all, s
         models[name]["cam"] = {
             "metric": f"{name}_gradcam_maps_per_s", "value": round(world * 64 * 20 / (msc * 1e-3), 1), "unit": "maps/s",
             "batch_per_gpu": 64, "ms_per_step": round(msc / 20, 4),
+            "latency_n1_ms": round(timed_steps(lambda: m.forward_cam(x1, None), 50, dev, 1, local) / 50, 4),
             "kernels": {c: {k2: v[k2] for k2 in ("ms", "launches", "GBps", "TFLOPs")}
                         for c, v in sorted(tabc.items(), key=lambda kv: -kv[1]["ms"]) if c.startswith("cam")}}
         del m
